@@ -1,0 +1,284 @@
+// oracle/ref_harness.cu -- TEST INFRASTRUCTURE ONLY (never linked into the product).
+//
+// Drives the UNMODIFIED reference renderer (sources compiled where they lie under
+// /root/reference, see oracle/Makefile) and dumps what the parity tests need:
+//   * the LBVH arrays right after PathtraceInit   (reference: src/bvh.cu:456-516)
+//   * per-bounce queues / counters / PathState     (reference loop: src/pathtrace_wavefront.cu:278-348)
+//   * the direct / indirect accumulators           (radiance = (direct+indirect)/iter, :74-75)
+// and times the reference's own wavefront / megakernel front-ends for the bench's
+// reference arm.
+//
+// The reference keeps its state in TU-local statics (`pState`, `hst_scene`,
+// pathtrace_wavefront.cu:118-120), so the only way to reach them without editing the
+// reference is textual inclusion of that TU plus an accessor in the same namespace.
+#include "pathtrace_wavefront.cu"   // resolved through -I$(REF)/src ; not a copy
+
+#include "pathtrace.h"
+#include <chrono>
+#include <string>
+#include <vector>
+#include <sys/stat.h>
+
+bool g_enableVisualization = false;   // extern in the reference (pathtrace_wavefront.cu:41); defined by the host app
+
+namespace pathtrace_wavefront {
+    WavefrontPathTracerState* OracleState() { return pState; }
+}
+
+static std::string g_out;
+
+static void dump_raw(const std::string& name, const void* host, size_t bytes) {
+    std::string p = g_out + "/" + name + ".bin";
+    FILE* f = fopen(p.c_str(), "wb");
+    if (!f) { fprintf(stderr, "refdump: cannot write %s\n", p.c_str()); exit(2); }
+    if (bytes) fwrite(host, 1, bytes, f);
+    fclose(f);
+}
+
+static void dump_dev(const std::string& name, const void* dev, size_t bytes) {
+    std::vector<unsigned char> h(bytes ? bytes : 1);
+    if (bytes) {
+        cudaError_t e = cudaMemcpy(h.data(), dev, bytes, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { fprintf(stderr, "refdump: D2H %s: %s\n", name.c_str(), cudaGetErrorString(e)); exit(3); }
+    }
+    dump_raw(name, h.data(), bytes);
+}
+
+static int read_counter(const int* d) {
+    int v = 0;
+    cudaMemcpy(&v, d, sizeof(int), cudaMemcpyDeviceToHost);
+    return v;
+}
+
+static void dump_scene_and_bvh(Scene* scene, WavefrontPathTracerState* st) {
+    const int N = st->d_mesh_data.num_triangles;
+    const int V = st->d_mesh_data.num_vertices;
+    dump_dev("mesh_pos", st->d_mesh_data.pos, sizeof(float4) * V);
+    dump_dev("mesh_nor", st->d_mesh_data.nor, sizeof(float4) * V);
+    dump_dev("mesh_tangent", st->d_mesh_data.tangent, sizeof(float4) * V);
+    dump_dev("mesh_uv", st->d_mesh_data.uv, sizeof(float2) * V);
+    dump_dev("mesh_indices_matid", st->d_mesh_data.indices_matid, sizeof(int4) * N);
+    dump_dev("mesh_nor_geom", st->d_mesh_data.nor_geom, sizeof(float4) * N);
+    dump_raw("materials", scene->materials.data(), sizeof(Material) * scene->materials.size());
+    dump_raw("light_tri_idx", scene->lightInfo.tri_idx.data(), sizeof(int) * scene->lightInfo.tri_idx.size());
+    dump_raw("light_cdf", scene->lightInfo.cdf.data(), sizeof(float) * scene->lightInfo.cdf.size());
+    if (scene->env_map.width > 0) {
+        dump_raw("env_probs", scene->env_map.probs.data(), sizeof(float) * scene->env_map.probs.size());
+        dump_raw("env_aliases", scene->env_map.aliases.data(), sizeof(int) * scene->env_map.aliases.size());
+    }
+
+    const LBVHData& b = st->d_bvh_data;
+    dump_dev("bvh_aabb_min", b.aabb_min, sizeof(float4) * 2 * N);
+    dump_dev("bvh_aabb_max", b.aabb_max, sizeof(float4) * 2 * N);
+    dump_dev("bvh_centroid", b.centroid, sizeof(float4) * 2 * N);
+    dump_dev("bvh_primitive_indices", b.primitive_indices, sizeof(int) * 2 * N);
+    dump_dev("bvh_morton_codes", b.morton_codes, sizeof(unsigned long long) * N);
+    dump_dev("bvh_child_nodes", b.child_nodes, sizeof(int2) * (N > 0 ? N - 1 : 0));
+    dump_dev("bvh_parent", b.parent, sizeof(int) * 2 * N);
+    dump_dev("bvh_escape_indices", b.escape_indices, sizeof(int) * 2 * N);
+    float world[8] = { b.world_aabb_min.x, b.world_aabb_min.y, b.world_aabb_min.z, b.world_aabb_min.w,
+                       b.world_aabb_max.x, b.world_aabb_max.y, b.world_aabb_max.z, b.world_aabb_max.w };
+    dump_raw("bvh_world_aabb", world, sizeof(world));
+
+    const Camera& c = scene->state.camera;
+    float cam[17] = { c.position.x, c.position.y, c.position.z, c.view.x, c.view.y, c.view.z,
+                      c.up.x, c.up.y, c.up.z, c.right.x, c.right.y, c.right.z,
+                      c.fov.x, c.fov.y, c.pixelLength.x, c.pixelLength.y, 0.0f };
+    dump_raw("camera", cam, sizeof(cam));
+
+    std::string p = g_out + "/meta.json";
+    FILE* f = fopen(p.c_str(), "w");
+    fprintf(f, "{\"num_triangles\": %d, \"num_vertices\": %d, \"width\": %d, \"height\": %d, "
+               "\"trace_depth\": %d, \"num_materials\": %d, \"num_lights\": %d, \"light_total_area\": %.9g, "
+               "\"num_textures\": %d, \"env_tex_id\": %d, \"pdf_map_id\": %d, \"env_width\": %d, \"env_height\": %d}\n",
+            N, V, c.resolution.x, c.resolution.y, scene->state.traceDepth, (int)scene->materials.size(),
+            scene->lightInfo.num_lights, scene->lightInfo.total_area, (int)scene->texture_handles.size(),
+            scene->env_map.env_tex_id, scene->env_map.pdf_map_id, scene->env_map.width, scene->env_map.height);
+    fclose(f);
+}
+
+static void dump_path_state(const std::string& tag, WavefrontPathTracerState* st, int P) {
+    const PathState& ps = st->d_path_state;
+    dump_dev(tag + "_ray_ori", ps.ray_ori, sizeof(float4) * P);
+    dump_dev(tag + "_ray_dir_dist", ps.ray_dir_dist, sizeof(float4) * P);
+    dump_dev(tag + "_hit_normal", ps.hit_normal, sizeof(float4) * P);
+    dump_dev(tag + "_throughput_pdf", ps.throughput_pdf, sizeof(float4) * P);
+    dump_dev(tag + "_hit_geom_id", ps.hit_geom_id, sizeof(int) * P);
+    dump_dev(tag + "_material_id", ps.material_id, sizeof(int) * P);
+    dump_dev(tag + "_pixel_idx", ps.pixel_idx, sizeof(int) * P);
+    dump_dev(tag + "_remaining_bounces", ps.remaining_bounces, sizeof(int) * P);
+    dump_dev(tag + "_rng_state", ps.rng_state, sizeof(unsigned int) * P);
+}
+
+// One frame, driving the reference's own stage wrappers in the order of
+// pathtrace_wavefront.cu:232-348 with dumps in between.
+static void staged_frame(Scene* scene, WavefrontPathTracerState* st, int iter, bool dump) {
+    using namespace pathtrace_wavefront;
+    const int trace_depth = scene->state.traceDepth;
+    const Camera& cam = scene->state.camera;
+    const int P = cam.resolution.x * cam.resolution.y;
+    if (iter == 1) {
+        cudaMemset(st->d_direct_image, 0, P * sizeof(glm::vec3));
+        cudaMemset(st->d_indirect_image, 0, P * sizeof(glm::vec3));
+        st->clear();
+        InitPathPoolKernel<<<(P + 127) / 128, 128>>>(st->d_path_state, P);
+    }
+    ray_gen::GeneratePathTracingRays(cam, trace_depth, iter, P, st);
+    if (dump) dump_path_state("raygen", st, P);
+
+    std::vector<int> counters;   // per step: n_ext, n_sh, n_pbr, n_diffuse, n_refl, n_refr
+    for (int step = 0; step < trace_depth; step++) {
+        char tag[32]; snprintf(tag, sizeof(tag), "s%d", step);
+        std::string T(tag);
+        int n_ext = read_counter(st->d_extension_ray_counter);
+        int n_sh = read_counter(st->d_shadow_queue_counter);
+        if (dump) {
+            dump_dev(T + "_ext_queue", st->d_extension_ray_queue, sizeof(int) * n_ext);
+            dump_dev(T + "_shadow_ori_tmax", st->d_shadow_queue.ray_ori_tmax, sizeof(float4) * n_sh);
+            dump_dev(T + "_shadow_dir", st->d_shadow_queue.ray_dir, sizeof(float4) * n_sh);
+            dump_dev(T + "_shadow_radiance", st->d_shadow_queue.radiance, sizeof(float4) * n_sh);
+            dump_dev(T + "_shadow_pixel", st->d_shadow_queue.pixel_idx, sizeof(int) * n_sh);
+        }
+        if (n_ext > 0) TraceExtensionRay(n_ext, st);
+        if (n_sh > 0) TraceShadowRay(n_sh, st);
+        if (dump) {
+            dump_path_state(T + "_traced", st, P);
+            dump_dev(T + "_direct", st->d_direct_image, sizeof(glm::vec3) * P);
+        }
+        st->resetCounters();
+        logic::RunPathLogic(P, trace_depth, st, make_float2(cam.resolution.x, cam.resolution.y));
+        int n_pbr = read_counter(st->d_pbr_counter);
+        int n_dif = read_counter(st->d_diffuse_counter);
+        int n_rfl = read_counter(st->d_reflection_counter);
+        int n_rfr = read_counter(st->d_refraction_counter);
+        if (dump) {
+            dump_dev(T + "_pbr_queue", st->d_pbr_queue, sizeof(int) * n_pbr);
+            dump_dev(T + "_diffuse_queue", st->d_diffuse_queue, sizeof(int) * n_dif);
+            dump_dev(T + "_reflection_queue", st->d_reflection_queue, sizeof(int) * n_rfl);
+            dump_dev(T + "_refraction_queue", st->d_refraction_queue, sizeof(int) * n_rfr);
+            dump_dev(T + "_indirect", st->d_indirect_image, sizeof(glm::vec3) * P);
+            dump_dev(T + "_logic_remaining_bounces", st->d_path_state.remaining_bounces, sizeof(int) * P);
+        }
+        // The reference sorts the PBR and diffuse queues by material id (:312-334); the
+        // order only changes which atomicAdd slot a path lands in, never a value.
+        if (n_pbr > 0) {
+            GenerateMaterialSortKeysKernel<<<(n_pbr + 127) / 128, 128>>>(st->d_pbr_queue, n_pbr, st->d_path_state, st->d_mat_sort_keys);
+            thrust::device_ptr<int> k(st->d_mat_sort_keys), v(st->d_pbr_queue);
+            thrust::sort_by_key(k, k + n_pbr, v);
+            shading::SamplePBR(n_pbr, trace_depth, st);
+        }
+        if (n_dif > 0) {
+            GenerateMaterialSortKeysKernel<<<(n_dif + 127) / 128, 128>>>(st->d_diffuse_queue, n_dif, st->d_path_state, st->d_mat_sort_keys);
+            thrust::device_ptr<int> k(st->d_mat_sort_keys), v(st->d_diffuse_queue);
+            thrust::sort_by_key(k, k + n_dif, v);
+            shading::SampleDiffuse(n_dif, trace_depth, st);
+        }
+        if (n_rfl > 0) shading::SampleSpecularReflection(n_rfl, trace_depth, st);
+        if (n_rfr > 0) shading::SampleSpecularRefraction(n_rfr, trace_depth, st);
+        if (dump) dump_path_state(T + "_shaded", st, P);
+        int c6[6] = { n_ext, n_sh, n_pbr, n_dif, n_rfl, n_rfr };
+        counters.insert(counters.end(), c6, c6 + 6);
+    }
+    st->prev_view_proj_mat = st->view_proj_mat;
+    if (dump) dump_raw("counters", counters.data(), sizeof(int) * counters.size());
+}
+
+static double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+int main(int argc, char** argv) {
+    if (argc < 3) {
+        fprintf(stderr,
+            "usage: refdump SCENE.json OUTDIR [--iters N] [--stages] [--selfcheck] [--bench K W] [--mega] [--no-dump]\n");
+        return 1;
+    }
+    std::string scene_file = argv[1];
+    g_out = argv[2];
+    int iters = 1, bench_k = 0, bench_w = 0;
+    bool stages = false, selfcheck = false, mega = false, no_dump = false;
+    for (int i = 3; i < argc; i++) {
+        std::string a = argv[i];
+        if (a == "--iters" && i + 1 < argc) iters = atoi(argv[++i]);
+        else if (a == "--stages") stages = true;
+        else if (a == "--selfcheck") selfcheck = true;
+        else if (a == "--mega") mega = true;
+        else if (a == "--no-dump") no_dump = true;
+        else if (a == "--bench" && i + 2 < argc) { bench_k = atoi(argv[++i]); bench_w = atoi(argv[++i]); }
+    }
+    mkdir(g_out.c_str(), 0777);
+    cudaSetDevice(0);
+    cudaFree(0);
+
+    Scene* scene = new Scene(scene_file);
+    const Camera& cam = scene->state.camera;
+    const int P = cam.resolution.x * cam.resolution.y;
+
+    GuiDataContainer gui;
+    gui.DenoiserOn = false;   // ctor default is true, which would switch the frame to SVGF 1-spp mode
+    gui.ShowBVH = false;      // left uninitialised by the reference ctor (utilities.h:32-38)
+
+    if (mega) {
+        pathtrace_megakernel::InitDataContainer(&gui);
+        pathtrace_megakernel::PathtraceInit(scene);
+        double mr = 0;
+        for (int i = 1; i <= bench_w; i++) pathtrace_megakernel::Pathtrace(NULL, 0, i);
+        cudaDeviceSynchronize();
+        double t0 = now_s();
+        for (int i = 1; i <= bench_k; i++) { pathtrace_megakernel::Pathtrace(NULL, 0, bench_w + i); mr += gui.MraysPerSec; }
+        cudaDeviceSynchronize();
+        double dt = now_s() - t0;
+        printf("REFBENCH {\"mode\": \"mega\", \"frames\": %d, \"ms_per_frame\": %.6f, \"mpaths_per_s\": %.6f, \"mrays_per_s\": %.6f}\n",
+               bench_k, dt * 1e3 / (bench_k > 0 ? bench_k : 1), bench_k * (double)P / dt / 1e6, mr / (bench_k > 0 ? bench_k : 1));
+        pathtrace_megakernel::PathtraceFree();
+        return 0;
+    }
+
+    pathtrace_wavefront::InitDataContainer(&gui);
+    double t_init0 = now_s();
+    pathtrace_wavefront::PathtraceInit(scene);
+    cudaDeviceSynchronize();
+    double t_init = now_s() - t_init0;
+    WavefrontPathTracerState* st = pathtrace_wavefront::OracleState();
+    if (!no_dump) dump_scene_and_bvh(scene, st);
+
+    if (bench_k > 0) {
+        double mr = 0;
+        for (int i = 1; i <= bench_w; i++) pathtrace_wavefront::Pathtrace(NULL, 0, i);
+        cudaDeviceSynchronize();
+        double t0 = now_s();
+        for (int i = 1; i <= bench_k; i++) { pathtrace_wavefront::Pathtrace(NULL, 0, bench_w + i); mr += gui.MraysPerSec; }
+        cudaDeviceSynchronize();
+        double dt = now_s() - t0;
+        printf("REFBENCH {\"mode\": \"wave\", \"frames\": %d, \"ms_per_frame\": %.6f, \"mpaths_per_s\": %.6f, \"mrays_per_s\": %.6f, \"init_s\": %.4f}\n",
+               bench_k, dt * 1e3 / bench_k, bench_k * (double)P / dt / 1e6, mr / bench_k, t_init);
+        pathtrace_wavefront::PathtraceFree();
+        return 0;
+    }
+
+    if (selfcheck) {
+        // harness-driven frames must reproduce the untouched Pathtrace() bit for bit
+        for (int i = 1; i <= iters; i++) pathtrace_wavefront::Pathtrace(NULL, 0, i);
+        cudaDeviceSynchronize();
+        std::vector<float> d0(3 * (size_t)P), i0(3 * (size_t)P), d1(3 * (size_t)P), i1(3 * (size_t)P);
+        cudaMemcpy(d0.data(), st->d_direct_image, sizeof(float) * 3 * P, cudaMemcpyDeviceToHost);
+        cudaMemcpy(i0.data(), st->d_indirect_image, sizeof(float) * 3 * P, cudaMemcpyDeviceToHost);
+        for (int i = 1; i <= iters; i++) staged_frame(scene, st, i, false);
+        cudaDeviceSynchronize();
+        cudaMemcpy(d1.data(), st->d_direct_image, sizeof(float) * 3 * P, cudaMemcpyDeviceToHost);
+        cudaMemcpy(i1.data(), st->d_indirect_image, sizeof(float) * 3 * P, cudaMemcpyDeviceToHost);
+        size_t bad = 0;
+        for (size_t k = 0; k < 3 * (size_t)P; k++)
+            if (memcmp(&d0[k], &d1[k], 4) || memcmp(&i0[k], &i1[k], 4)) bad++;
+        printf("REFSELFCHECK {\"iters\": %d, \"mismatching_floats\": %zu}\n", iters, bad);
+    }
+
+    for (int i = 1; i <= iters; i++) staged_frame(scene, st, i, stages && i == iters);
+    cudaDeviceSynchronize();
+    dump_dev("direct", st->d_direct_image, sizeof(glm::vec3) * P);
+    dump_dev("indirect", st->d_indirect_image, sizeof(glm::vec3) * P);
+    cudaError_t e = cudaGetLastError();
+    printf("REFDUMP {\"iters\": %d, \"pixels\": %d, \"cuda\": \"%s\"}\n", iters, P, cudaGetErrorString(e));
+    pathtrace_wavefront::PathtraceFree();
+    return e == cudaSuccess ? 0 : 4;
+}
