@@ -1,0 +1,178 @@
+// common.cuh -- device-side types shared by every kernel of the wavefront core.
+//
+// Arithmetic contract.  Radiance parity with the reference (per-pixel rel. err <= 1e-4 at 1 spp)
+// needs the same DECISIONS per path, so the float expressions here keep the reference's shape:
+// `V3` mirrors glm::vec3 component-wise operators, and the three primitives whose contraction
+// was read off the reference's sm_100 SASS are pinned with explicit intrinsics:
+//   dot(a,b)   = fma(a.z,b.z, fma(a.x,b.x, a.y*b.y))      GLM (x*x' + y*y') + z*z' after nvcc -fmad
+//   cross(a,b) = fma(a.y,b.z, -(b.y*a.z)), ...            first product fused, second rounded
+//   normalize  = v * (1 / sqrt(dot(v,v)))                 IEEE sqrt and reciprocal
+// (reference: external/include/glm/detail/func_geometric.inl:65-72,134-142,154-159; SASS of
+// src/intersections.cu:10-32 and src/kernels/ray_gen.cu:60-63.)
+#pragma once
+#include <cuda_runtime.h>
+#include <cfloat>
+#include <cstdint>
+
+#include "../../../include/ptb200.h"
+
+namespace ptb {
+
+#define PTB_PI 3.1415926535897932384626422832795028841971f      /* src/common/utilities.h:12 */
+#define PTB_TWO_PI 6.2831853071795864769252867665590057683943f  /* :13 */
+#define PTB_EPSILON 0.001f                                       /* :15 */
+#define PTB_INV_PI 0.31830988618f                                /* :16 */
+#define PTB_INV_TWO_PI 0.15915494309189533577f                   /* :17 */
+#define PTB_PDF_DIRAC_DELTA 1e10f                                /* :18 */
+
+enum { MAT_PBR = 0, MAT_DIFFUSE = 1, MAT_REFLECT = 2, MAT_REFRACT = 3 };
+
+struct V3 {
+    float x, y, z;
+    __host__ __device__ V3() {}
+    __host__ __device__ V3(float a, float b, float c) : x(a), y(b), z(c) {}
+    __host__ __device__ explicit V3(float a) : x(a), y(a), z(a) {}
+};
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return V3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return V3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator-(V3 a) { return V3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return V3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ V3 operator*(V3 a, float s) { return V3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return V3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ V3 operator/(V3 a, float s) { return V3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ V3 operator+(V3 a, float s) { return V3(a.x + s, a.y + s, a.z + s); }
+__device__ __forceinline__ V3 make_v3(float4 f) { return V3(f.x, f.y, f.z); }
+
+__device__ __forceinline__ float dot3(V3 a, V3 b) {
+    return __fmaf_rn(a.z, b.z, __fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)));
+}
+__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
+    return V3(__fmaf_rn(a.y, b.z, -__fmul_rn(b.y, a.z)),
+              __fmaf_rn(a.z, b.x, -__fmul_rn(b.z, a.x)),
+              __fmaf_rn(a.x, b.y, -__fmul_rn(b.x, a.y)));
+}
+__device__ __forceinline__ float length3(V3 v) { return __fsqrt_rn(dot3(v, v)); }
+__device__ __forceinline__ V3 normalize3(V3 v) {
+    float inv = __frcp_rn(__fsqrt_rn(dot3(v, v)));
+    return V3(__fmul_rn(v.x, inv), __fmul_rn(v.y, inv), __fmul_rn(v.z, inv));
+}
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }   // glm::clamp = min(max(x,lo),hi)
+__device__ __forceinline__ float mixf(float a, float b, float t) { return a * (1.0f - t) + b * t; }        // glm::mix: x*(1-a) + y*a
+
+// ---- RNG (src/rng.h:6-27) ---------------------------------------------------------------------
+__host__ __device__ __forceinline__ uint32_t wang_hash(uint32_t seed) {
+    seed = (seed ^ 61u) ^ (seed >> 16);
+    seed *= 9u;
+    seed = seed ^ (seed >> 4);
+    seed *= 0x27d4eb2du;
+    seed = seed ^ (seed >> 15);
+    return seed;
+}
+__device__ __forceinline__ float rand_float(uint32_t& state) {
+    state ^= state << 13;
+    state ^= state >> 17;
+    state ^= state << 5;
+    return __fmul_rn(__uint2float_rn(state), 2.3283064365386963e-10f);
+}
+
+// ---- scene on the device ------------------------------------------------------------------------
+struct MeshDev {                 // MeshData, src/scene_structs.h:134-149
+    const float4* pos;
+    const float4* nor;
+    const float4* tangent;
+    const float2* uv;
+    const int4* indices_matid;
+    const float4* nor_geom;
+    int num_vertices, num_triangles;
+};
+
+struct LightDev {                // LightData, src/scene_structs.h:76-81
+    const int* tri_idx;
+    const float* cdf;
+    int num_lights;
+    float total_area;
+};
+
+// LBVH in the reference's layout (LBVHData, src/scene_structs.h:151-169) -- what parity reads.
+struct LbvhRef {
+    float4* aabb_min;
+    float4* aabb_max;
+    float4* centroid;
+    int* primitive_indices;
+    unsigned long long* morton_codes;
+    int2* child_nodes;
+    int* parent;
+    int* escape_indices;
+    float4* world_aabb;          // [2] min, max (device copy; the reference keeps these on the host)
+};
+
+// Traversal layout derived from it (DESIGN.md "compressed node layout"): one 64-byte record per
+// internal node holding BOTH children's boxes and links, so a node visit is four coalescable
+// 16-byte loads from one 64-byte line instead of the reference's int2 + 4 scattered float4
+// (src/kernels/ray_cast.cu:78-88).  Leaves carry their three vertices inline (48 bytes), which
+// removes the primitive_indices -> indices_matid -> pos chain (:55-63).
+//   node[4*i+0] = (left.min.xyz , bits(left link))     link >= 0 : internal node index
+//   node[4*i+1] = (left.max.xyz , bits(right link))    link <  0 : ~(sorted leaf position)
+//   node[4*i+2] = (right.min.xyz, 0)
+//   node[4*i+3] = (right.max.xyz, 0)
+//   tri[3*k+0]  = (v0.xyz, bits(triangle index)), tri[3*k+1] = (v1.xyz,0), tri[3*k+2] = (v2.xyz,0)
+struct BvhDev {
+    const float4* node;
+    const float4* tri;
+    float4 root_min, root_max;   // AABB of node 0 (the root test of src/kernels/ray_cast.cu:40-47)
+    int num_triangles;
+};
+
+struct TexturesDev {
+    const cudaTextureObject_t* handles;
+    int env_tex_id, pdf_map_id;  // EnvMapAliasTable ids, src/scene_structs.h:67-74
+};
+
+// ---- path pool and queues -----------------------------------------------------------------------
+// PathState (src/scene_structs.h:97-117).  Slot == index into this renderer's owned pixels; the
+// GLOBAL pixel index (what seeds the RNG and what the reference calls pixel_idx) is derived from
+// the slot by TileMap, so it is not stored.
+struct PathPool {
+    float4* ray_ori;
+    float4* ray_dir_dist;
+    float4* hit_uv;              // the reference's `hit_normal`: (u, v, 0, 0) (src/kernels/ray_cast.cu:120)
+    float4* throughput_pdf;
+    int* hit_geom_id;
+    int* material_id;
+    int* remaining_bounces;
+    uint32_t* rng_state;
+};
+
+struct ShadowQueueDev {          // ShadowQueue, src/scene_structs.h:121-131
+    float4* ray_ori_tmax;
+    float4* ray_dir;
+    float4* radiance;
+    int* slot;                   // path slot (== local pixel) the radiance is added to
+};
+
+// Per-bounce counters, device resident for the whole frame (the reference reads six of them
+// back to the host every bounce, src/pathtrace_wavefront.cu:286-343).
+enum { CTR_EXT = 0, CTR_SHADOW = 1, CTR_PBR = 2, CTR_DIFFUSE = 3, CTR_REFLECT = 4, CTR_REFRACT = 5, CTR_STRIDE = 8 };
+
+struct TileMap {                 // rank r owns rows y with (y / stripe_rows) % world == r
+    int width, height;
+    int rank, world, stripe_rows;
+    int owned_pixels;
+    __host__ __device__ int global_pixel(int slot) const {
+        if (world <= 1) return slot;
+        int local_row = slot / width;
+        int x = slot - local_row * width;
+        int stripe_local = local_row / stripe_rows;
+        int row_in = local_row - stripe_local * stripe_rows;
+        int y = (stripe_local * world + rank) * stripe_rows + row_in;
+        return y * width + x;
+    }
+};
+
+struct CameraDev {               // Camera, src/scene_structs.h:16-26 (members the kernels read)
+    int res_x, res_y;
+    float pos[3], view[3], up[3], right[3];
+    float pixel_length[2];
+};
+
+}  // namespace ptb
