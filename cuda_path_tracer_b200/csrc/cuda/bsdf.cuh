@@ -1,0 +1,258 @@
+// bsdf.cuh -- material models and light sampling of the Shading stage.
+// Same models and the same float expression shapes as the reference (src/interactions.cu), so
+// that nvcc's FMA contraction lands on the same operations and per-path decisions (lobe choice,
+// reflect vs. refract, back-face kills) agree with the reference sample by sample.
+#pragma once
+#include "common.cuh"
+
+namespace ptb {
+
+struct Mat {          // `Material`, src/scene_structs.h:52-65
+    Vec3 basecolor;
+    float metallic, roughness, emittance, ior;
+    int type, diffuse_tex, normal_tex, mr_tex;
+};
+
+__device__ __forceinline__ Mat load_material(const ptb_material* __restrict__ mats, int id) {
+    const float4* p = reinterpret_cast<const float4*>(mats + id);
+    float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    Mat m;
+    m.basecolor = Vec3(a.x, a.y, a.z);
+    m.metallic = a.w;
+    m.roughness = b.x; m.emittance = b.y; m.ior = b.z; m.type = __float_as_int(b.w);
+    m.diffuse_tex = __float_as_int(c.x); m.normal_tex = __float_as_int(c.y); m.mr_tex = __float_as_int(c.z);
+    return m;
+}
+
+// LocalToWorld, src/interactions.cu:6-15
+__device__ __forceinline__ Vec3 local_to_world(Vec3 l, Vec3 N) {
+    Vec3 helper;
+    if (fabsf(N.x) < 0.57735027f) helper = Vec3(1.0f, 0.0f, 0.0f);
+    else if (fabsf(N.y) < 0.57735027f) helper = Vec3(0.0f, 1.0f, 0.0f);
+    else helper = Vec3(0.0f, 0.0f, 1.0f);
+    Vec3 T = normalize3(cross3(N, helper));
+    Vec3 B = normalize3(cross3(N, T));
+    return T * l.x + B * l.y + N * l.z;
+}
+
+// FresnelSchlick, src/interactions.cu:17-27
+__device__ __forceinline__ Vec3 fresnel_schlick3(Vec3 F0, float cos_theta) {
+    float x = clampf(1.0f - cos_theta, 0.0f, 1.0f);
+    float x5 = x * x * x * x * x;
+    return F0 + (Vec3(1.0f) - F0) * x5;
+}
+__device__ __forceinline__ float fresnel_schlick1(float F0, float cos_theta) {
+    float x = clampf(1.0f - cos_theta, 0.0f, 1.0f);
+    float x5 = x * x * x * x * x;
+    return F0 + (1.0f - F0) * x5;
+}
+
+// DistributionGGX, src/interactions.cu:29-37
+__device__ __forceinline__ float ggx_d(Vec3 N, Vec3 H, float roughness) {
+    float a = roughness * roughness;
+    float a2 = a * a;
+    float NdotH = fmaxf(dot3(N, H), 0.0f);
+    float NdotH2 = NdotH * NdotH;
+    float denom = (NdotH2 * (a2 - 1.0f) + 1.0f);
+    denom = PTB_PI * denom * denom;
+    return a2 / fmaxf(denom, 0.0000001f);
+}
+
+// GeometrySchlickGGX / GeometrySmith, src/interactions.cu:39-51
+__device__ __forceinline__ float smith_g1(float NdotV, float roughness) {
+    float r = roughness + 1.0f;
+    float k = (r * r) / 8.0f;
+    return NdotV / (NdotV * (1.0f - k) + k);
+}
+__device__ __forceinline__ float smith_g(Vec3 N, Vec3 V, Vec3 L, float roughness) {
+    float NdotV = fmaxf(dot3(N, V), 0.0f);
+    float NdotL = fmaxf(dot3(N, L), 0.0f);
+    float ggx2 = smith_g1(NdotV, roughness);
+    float ggx1 = smith_g1(NdotL, roughness);
+    return ggx1 * ggx2;
+}
+
+// CosineWeightedSampling, src/interactions.cu:53-61
+__device__ __forceinline__ Vec3 sample_cosine(Vec3 N, float xi_x, float xi_y) {
+    float up = sqrtf(xi_x);
+    float over = sqrtf(1.0f - up * up);
+    float around = xi_y * PTB_TWO_PI;
+    Vec3 l(cosf(around) * over, sinf(around) * over, up);
+    return local_to_world(l, N);
+}
+
+// NDFImportanceSampling, src/interactions.cu:63-76
+__device__ __forceinline__ Vec3 sample_ggx_reflect(Vec3 N, Vec3 wo, float roughness, float xi_x, float xi_y) {
+    float a = roughness * roughness;
+    float phi = PTB_TWO_PI * xi_x;
+    float cos_theta = sqrtf((1.0f - xi_y) / (1.0f + (a * a - 1.0f) * xi_y));
+    float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+    Vec3 h_local(sin_theta * cosf(phi), sin_theta * sinf(phi), cos_theta);
+    Vec3 H = local_to_world(h_local, N);
+    return reflect3(-wo, H);
+}
+
+// CalculateSpecularProbability, src/interactions.cu:80-90
+__device__ __forceinline__ float specular_probability(const Mat& m, Vec3 N, Vec3 V) {
+    Vec3 F0 = mix3(Vec3(0.04f), m.basecolor, m.metallic);
+    Vec3 F = fresnel_schlick3(F0, fmaxf(dot3(N, V), 0.0f));
+    float p = (F.x + F.y + F.z) / 3.0f;
+    p = mixf(p, 1.0f, m.metallic);
+    return clampf(p, 0.001f, 0.999f);
+}
+
+// evalPBR, src/interactions.cu:96-124
+__device__ __forceinline__ Vec3 eval_pbr(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+    float NdotL = dot3(N, wi);
+    float NdotV = dot3(N, wo);
+    if (NdotL <= 0.0f) return Vec3(0.0f);
+    Vec3 H = normalize3(wo + wi);
+    float VdotH = fmaxf(dot3(wo, H), 0.0f);
+    float roughness = clampf(m.roughness, 0.01f, 1.0f);
+    Vec3 F0 = mix3(Vec3(0.04f), m.basecolor, m.metallic);
+    Vec3 F = fresnel_schlick3(F0, VdotH);
+    float D = ggx_d(N, H, roughness);
+    float G = smith_g(N, wo, wi, roughness);
+    Vec3 numerator = D * G * F;
+    float denominator = 4.0f * NdotV * NdotL + PTB_EPSILON;
+    Vec3 specular = numerator / denominator;
+    Vec3 kD = Vec3(1.0f) - F;
+    kD = kD * (1.0f - m.metallic);
+    Vec3 diffuse = kD * m.basecolor * PTB_INV_PI;
+    return diffuse + specular;
+}
+
+// pdfPBR, src/interactions.cu:148-171
+__device__ __forceinline__ float pdf_pbr(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+    float NdotL = dot3(N, wi);
+    if (NdotL <= 0.0f) return 0.0f;
+    Vec3 H = normalize3(wo + wi);
+    float VdotH = fmaxf(dot3(wo, H), 0.0f);
+    float roughness = clampf(m.roughness, 0.01f, 1.0f);
+    float pdf_diff = NdotL * PTB_INV_PI;
+    float D = ggx_d(N, H, roughness);
+    float NdotH = fmaxf(dot3(N, H), 0.0f);
+    float pdf_spec = (D * NdotH) / (4.0f * VdotH + 0.0000001f);
+    float spec_prob = specular_probability(m, N, wo);
+    float diff_prob = 1.0f - spec_prob;
+    return spec_prob * pdf_spec + diff_prob * pdf_diff;
+}
+
+// evalBSDF / pdfBSDF for the two materials that do NEE (src/interactions.cu:191-216)
+__device__ __forceinline__ Vec3 eval_bsdf(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+    if (m.type == MAT_PBR) return eval_pbr(wo, wi, N, m);
+    if (m.type == MAT_DIFFUSE) return m.basecolor * PTB_INV_PI;
+    return Vec3(0.0f);
+}
+__device__ __forceinline__ float pdf_diffuse(Vec3 wi, Vec3 N) {
+    float NdotL = dot3(N, wi);
+    if (NdotL <= 0.0f) return 0.0f;
+    return NdotL * PTB_INV_PI;
+}
+__device__ __forceinline__ float pdf_bsdf(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+    if (m.type == MAT_PBR) return pdf_pbr(wo, wi, N, m);
+    if (m.type == MAT_DIFFUSE) return pdf_diffuse(wi, N);
+    return PTB_PDF_DIRAC_DELTA;
+}
+
+// samplePBR, src/interactions.cu:223-253.  Draw order is the DEVICE order of the reference
+// build: xi.x = 1st draw, xi.y = 2nd, lobe selector = 3rd.
+__device__ __forceinline__ Vec3 sample_pbr(Vec3 wo, Vec3& wi, float& pdf, Vec3 N, const Mat& m, uint32_t& seed) {
+    float xi_x = rand_float(seed);
+    float xi_y = rand_float(seed);
+    float r_select = rand_float(seed);
+    float roughness = clampf(m.roughness, 0.01f, 1.0f);
+    float spec_prob = specular_probability(m, N, wo);
+    if (r_select < spec_prob) wi = sample_ggx_reflect(N, wo, roughness, xi_x, xi_y);
+    else wi = sample_cosine(N, xi_x, xi_y);
+    wi = normalize3(wi);
+    if (dot3(N, wi) <= 0.0f) { pdf = 0.0f; return Vec3(0.0f); }
+    pdf = pdf_pbr(wo, wi, N, m);
+    Vec3 fr = eval_pbr(wo, wi, N, m);
+    return fr * fmaxf(0.0f, dot3(N, wi)) / fmaxf(pdf, PTB_EPSILON);
+}
+
+// sampleDiffuse, src/interactions.cu:323-338
+__device__ __forceinline__ Vec3 sample_diffuse(Vec3& wi, float& pdf, Vec3 N, const Mat& m, uint32_t& seed) {
+    float xi_x = rand_float(seed);
+    float xi_y = rand_float(seed);
+    wi = sample_cosine(N, xi_x, xi_y);
+    if (dot3(N, wi) <= 0.0f) { pdf = 0.0f; return Vec3(0.0f); }
+    pdf = pdf_diffuse(wi, N);
+    Vec3 fr = m.basecolor * PTB_INV_PI;
+    return fr * fmaxf(0.0f, dot3(N, wi)) / fmaxf(pdf, PTB_EPSILON);
+}
+
+// sampleSpecularReflection, src/interactions.cu:340-354
+__device__ __forceinline__ Vec3 sample_mirror(Vec3 wo, Vec3& wi, float& pdf, Vec3 N, const Mat& m) {
+    wi = reflect3(-wo, N);
+    float NdotWi = fmaxf(dot3(N, wi), 0.0f);
+    pdf = PTB_PDF_DIRAC_DELTA;
+    Vec3 F0 = mix3(Vec3(0.04f), m.basecolor, m.metallic);
+    return fresnel_schlick3(F0, NdotWi);
+}
+
+// sampleSpecularRefraction, src/interactions.cu:356-397; glm::refract per
+// external/include/glm/detail/func_geometric.inl:194-200.
+__device__ __forceinline__ Vec3 sample_dielectric(Vec3 wo, Vec3& wi, float& pdf, Vec3 N, const Mat& m, uint32_t& seed) {
+    float n1 = 1.0f, n2 = m.ior;
+    Vec3 n_eff = N;
+    if (dot3(wo, N) < 0.0f) { n1 = m.ior; n2 = 1.0f; n_eff = -N; }
+    float eta = n1 / n2;
+    float cos_i = clampf(dot3(wo, n_eff), 0.0f, 1.0f);
+    float r0 = (n1 - n2) / (n1 + n2);
+    r0 *= r0;
+    float Fr = fresnel_schlick1(r0, cos_i);
+    float sin_i2 = fmaxf(0.0f, 1.0f - cos_i * cos_i);
+    float sin_t2 = eta * eta * sin_i2;
+    float rnd = rand_float(seed);
+    pdf = PTB_PDF_DIRAC_DELTA;
+    if (sin_t2 >= 1.0f || rnd < Fr) {
+        wi = reflect3(-wo, n_eff);
+        return Vec3(1.0f);
+    }
+    Vec3 I = -wo;
+    float d = dot3(n_eff, I);
+    float k = 1.0f - eta * eta * (1.0f - d * d);
+    wi = (eta * I - (eta * d + sqrtf(k)) * n_eff) * (float)(k >= 0.0f);
+    float factor = (n2 * n2) / (n1 * n1);
+    return m.basecolor * factor;
+}
+
+// BinarySearch, src/common/cuda_utilities.h:199-214
+__device__ __forceinline__ int cdf_search(const float* __restrict__ cdf, int count, float value) {
+    int left = 0, right = count - 1;
+    while (left <= right) {
+        int mid = left + (right - left) / 2;
+        if (__ldg(&cdf[mid]) < value) left = mid + 1;
+        else right = mid - 1;
+    }
+    return min(left, count - 1);
+}
+
+// SampleLight, src/interactions.cu:400-445
+__device__ __forceinline__ void sample_light(const MeshDev& mesh, const LightDev& lights, uint32_t& seed,
+                                             Vec3& point, Vec3& normal, float& pdf_area, int& tri_index) {
+    float r1 = rand_float(seed);
+    float r2 = rand_float(seed);
+    float r3 = rand_float(seed);
+    int ci = cdf_search(lights.cdf, lights.num_lights, r1);
+    tri_index = __ldg(&lights.tri_idx[ci]);
+    int4 im = __ldg(&mesh.indices_matid[tri_index]);
+    Vec3 p0 = make_v3(__ldg(&mesh.pos[im.x])), p1 = make_v3(__ldg(&mesh.pos[im.y])), p2 = make_v3(__ldg(&mesh.pos[im.z]));
+    float sqrt_r2 = sqrtf(r2);
+    float b_u = 1.0f - sqrt_r2;
+    float b_v = r3 * sqrt_r2;
+    point = p0 * b_u + p1 * b_v + p2 * (1.0f - b_u - b_v);
+    normal = normalize3(cross3(p1 - p0, p2 - p0));
+    pdf_area = 1.0f / lights.total_area;
+}
+
+// PowerHeuristic, src/common/cuda_utilities.h:193-197
+__device__ __forceinline__ float power_heuristic(float f, float g) {
+    float f2 = f * f;
+    float g2 = g * g;
+    return f2 / (f2 + g2 + 1e-5f);
+}
+
+}  // namespace ptb

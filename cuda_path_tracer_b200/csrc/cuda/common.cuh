@@ -2,7 +2,7 @@
 //
 // Arithmetic contract.  Radiance parity with the reference (per-pixel rel. err <= 1e-4 at 1 spp)
 // needs the same DECISIONS per path, so the float expressions here keep the reference's shape:
-// `V3` mirrors glm::vec3 component-wise operators, and the three primitives whose contraction
+// `Vec3` mirrors glm::vec3 component-wise operators, and the three primitives whose contraction
 // was read off the reference's sm_100 SASS are pinned with explicit intrinsics:
 //   dot(a,b)   = fma(a.z,b.z, fma(a.x,b.x, a.y*b.y))      GLM (x*x' + y*y') + z*z' after nvcc -fmad
 //   cross(a,b) = fma(a.y,b.z, -(b.y*a.z)), ...            first product fused, second rounded
@@ -27,37 +27,46 @@ namespace ptb {
 
 enum { MAT_PBR = 0, MAT_DIFFUSE = 1, MAT_REFLECT = 2, MAT_REFRACT = 3 };
 
-struct V3 {
+struct Vec3 {
     float x, y, z;
-    __host__ __device__ V3() {}
-    __host__ __device__ V3(float a, float b, float c) : x(a), y(b), z(c) {}
-    __host__ __device__ explicit V3(float a) : x(a), y(a), z(a) {}
+    __host__ __device__ Vec3() {}
+    __host__ __device__ Vec3(float a, float b, float c) : x(a), y(b), z(c) {}
+    __host__ __device__ explicit Vec3(float a) : x(a), y(a), z(a) {}
 };
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return V3(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return V3(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ V3 operator-(V3 a) { return V3(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ V3 operator*(V3 a, V3 b) { return V3(a.x * b.x, a.y * b.y, a.z * b.z); }
-__device__ __forceinline__ V3 operator*(V3 a, float s) { return V3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ V3 operator*(float s, V3 a) { return V3(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ V3 operator/(V3 a, float s) { return V3(a.x / s, a.y / s, a.z / s); }
-__device__ __forceinline__ V3 operator+(V3 a, float s) { return V3(a.x + s, a.y + s, a.z + s); }
-__device__ __forceinline__ V3 make_v3(float4 f) { return V3(f.x, f.y, f.z); }
+__device__ __forceinline__ Vec3 operator+(Vec3 a, Vec3 b) { return Vec3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ Vec3 operator-(Vec3 a, Vec3 b) { return Vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ Vec3 operator-(Vec3 a) { return Vec3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, Vec3 b) { return Vec3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, float s) { return Vec3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ Vec3 operator*(float s, Vec3 a) { return Vec3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ Vec3 operator/(Vec3 a, float s) { return Vec3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ Vec3 operator+(Vec3 a, float s) { return Vec3(a.x + s, a.y + s, a.z + s); }
+__device__ __forceinline__ Vec3 make_v3(float4 f) { return Vec3(f.x, f.y, f.z); }
 
-__device__ __forceinline__ float dot3(V3 a, V3 b) {
+__device__ __forceinline__ float dot3(Vec3 a, Vec3 b) {
     return __fmaf_rn(a.z, b.z, __fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)));
 }
-__device__ __forceinline__ V3 cross3(V3 a, V3 b) {
-    return V3(__fmaf_rn(a.y, b.z, -__fmul_rn(b.y, a.z)),
+__device__ __forceinline__ Vec3 cross3(Vec3 a, Vec3 b) {
+    return Vec3(__fmaf_rn(a.y, b.z, -__fmul_rn(b.y, a.z)),
               __fmaf_rn(a.z, b.x, -__fmul_rn(b.z, a.x)),
               __fmaf_rn(a.x, b.y, -__fmul_rn(b.x, a.y)));
 }
-__device__ __forceinline__ float length3(V3 v) { return __fsqrt_rn(dot3(v, v)); }
-__device__ __forceinline__ V3 normalize3(V3 v) {
+__device__ __forceinline__ float length3(Vec3 v) { return __fsqrt_rn(dot3(v, v)); }
+__device__ __forceinline__ Vec3 normalize3(Vec3 v) {
     float inv = __frcp_rn(__fsqrt_rn(dot3(v, v)));
-    return V3(__fmul_rn(v.x, inv), __fmul_rn(v.y, inv), __fmul_rn(v.z, inv));
+    return Vec3(__fmul_rn(v.x, inv), __fmul_rn(v.y, inv), __fmul_rn(v.z, inv));
 }
-__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }   // glm::clamp = min(max(x,lo),hi)
-__device__ __forceinline__ float mixf(float a, float b, float t) { return a * (1.0f - t) + b * t; }        // glm::mix: x*(1-a) + y*a
+// glm::min / glm::max / glm::clamp (detail/func_common.inl:409-456): plain comparisons, so a NaN
+// argument propagates the way it does in the reference (fminf/fmaxf would drop it).
+__device__ __forceinline__ float glm_min(float x, float y) { return x < y ? x : y; }
+__device__ __forceinline__ float glm_max(float x, float y) { return x > y ? x : y; }
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return glm_min(glm_max(x, lo), hi); }
+// glm::mix (detail/func_common.inl:74-105): x + a * (y - x)
+__device__ __forceinline__ float mixf(float x, float y, float a) { return x + a * (y - x); }
+__device__ __forceinline__ Vec3 mix3(Vec3 x, Vec3 y, float a) { return x + a * (y - x); }
+__device__ __forceinline__ Vec3 operator/(Vec3 a, Vec3 b) { return Vec3(a.x / b.x, a.y / b.y, a.z / b.z); }
+// glm::reflect (detail/func_geometric.inl:176-180): I - N * dot(N, I) * 2
+__device__ __forceinline__ Vec3 reflect3(Vec3 I, Vec3 N) { return I - N * dot3(N, I) * 2.0f; }
 
 // ---- RNG (src/rng.h:6-27) ---------------------------------------------------------------------
 __host__ __device__ __forceinline__ uint32_t wang_hash(uint32_t seed) {

@@ -1,0 +1,147 @@
+// raycast.cuh -- BVH traversal primitives of the RayCast stage (device functions).
+//
+// Same tree and the same visiting ORDER as the reference's closest-hit walk
+// (src/kernels/ray_cast.cu:26-107): near child first, ties go right, strict `t < t_min`, and the
+// walk stops when 32 entries are stacked.  With identical slab / triangle arithmetic this makes
+// the winning triangle, t and (u, v) bit-identical, including for equal-t ties on shared edges.
+// What changes is the memory side: one 64-byte node record per internal node (4 x LDG.128 from
+// one line, instead of int2 + 4 scattered float4), vertices inline in the leaf (3 x LDG.128,
+// instead of primitive_indices -> indices_matid -> 3 x pos), the stack in shared memory instead of
+// local memory, and no function calls (the reference's two tests are __noinline__).
+#pragma once
+#include "common.cuh"
+
+namespace ptb {
+
+#define PTB_NODE_NONE 0x7fffffff
+#define PTB_EXT_STACK 32          /* src/kernels/ray_cast.cu:35,106 */
+#define PTB_SHADOW_STACK 64
+#define PTB_RC_THREADS 128
+
+// BoudingboxIntersetionTest, src/intersections.cu:34-61 (FADD, FMUL, min/max chain; no FMA).
+__device__ __forceinline__ float slab_test(float4 mn, float4 mx, Vec3 o, Vec3 inv) {
+    float t1x = __fmul_rn(__fsub_rn(mn.x, o.x), inv.x);
+    float t2x = __fmul_rn(__fsub_rn(mx.x, o.x), inv.x);
+    float t_near = fminf(t1x, t2x);
+    float t_far = fmaxf(t1x, t2x);
+    float t1y = __fmul_rn(__fsub_rn(mn.y, o.y), inv.y);
+    float t2y = __fmul_rn(__fsub_rn(mx.y, o.y), inv.y);
+    t_near = fmaxf(t_near, fminf(t1y, t2y));
+    t_far = fminf(t_far, fmaxf(t1y, t2y));
+    float t1z = __fmul_rn(__fsub_rn(mn.z, o.z), inv.z);
+    float t2z = __fmul_rn(__fsub_rn(mx.z, o.z), inv.z);
+    t_near = fmaxf(t_near, fminf(t1z, t2z));
+    t_far = fminf(t_far, fmaxf(t1z, t2z));
+    if (t_near <= t_far && t_far > 0.0f) return fmaxf(0.0f, t_near);
+    return -1.0f;
+}
+
+// TriangleIntersectionTest, src/intersections.cu:10-32, in the contraction the reference's sm_100
+// SASS shows: cross = fma(a,b,-(c*d)), dot = fma(z, fma(x, y*y')), then a
+// separate multiply by the IEEE reciprocal of det.
+__device__ __forceinline__ float triangle_test(Vec3 v0, Vec3 v1, Vec3 v2, Vec3 o, Vec3 d, float& out_u, float& out_v) {
+    Vec3 e1(__fsub_rn(v1.x, v0.x), __fsub_rn(v1.y, v0.y), __fsub_rn(v1.z, v0.z));
+    Vec3 e2(__fsub_rn(v2.x, v0.x), __fsub_rn(v2.y, v0.y), __fsub_rn(v2.z, v0.z));
+    Vec3 pvec = cross3(d, e2);
+    float det = dot3(e1, pvec);
+    if (fabsf(det) < PTB_EPSILON) return -1.0f;
+    float inv_det = __frcp_rn(det);
+    Vec3 tvec(__fsub_rn(o.x, v0.x), __fsub_rn(o.y, v0.y), __fsub_rn(o.z, v0.z));
+    out_u = __fmul_rn(dot3(tvec, pvec), inv_det);
+    if (out_u < 0.0f || out_u > 1.0f) return -1.0f;
+    Vec3 qvec = cross3(tvec, e1);
+    out_v = __fmul_rn(dot3(d, qvec), inv_det);
+    if (out_v < 0.0f || __fadd_rn(out_u, out_v) > 1.0f) return -1.0f;
+    float t = __fmul_rn(dot3(e2, qvec), inv_det);
+    return (t > 1e-7f) ? t : -1.0f;
+}
+
+struct Hit {
+    int prim;      // triangle index, -1 = miss
+    int mat;       // material id of the hit triangle
+    float t, u, v;
+};
+
+// Closest hit.  `stack` points at this thread's column of a [PTB_EXT_STACK][blockDim] shared array.
+__device__ __forceinline__ Hit trace_closest(const BvhDev& bvh, Vec3 o, Vec3 d, int* stack, int stride) {
+    Vec3 inv(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));   // 1.0f / ray.direction, :29
+    Hit h;
+    h.prim = -1; h.mat = -1; h.t = FLT_MAX; h.u = 0.0f; h.v = 0.0f;
+    int sp = 0;
+    int node = (slab_test(bvh.root_min, bvh.root_max, o, inv) == -1.0f) ? PTB_NODE_NONE : 0;
+    while (node != PTB_NODE_NONE || sp > 0) {
+        if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
+        if (node < 0) {
+            const float4* tp = bvh.tri + 3 * (size_t)(~node);
+            float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            float u, v;
+            float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, u, v);
+            if (t > PTB_EPSILON && t < h.t) {
+                h.t = t; h.u = u; h.v = v;
+                h.prim = __float_as_int(a.w);
+                h.mat = __float_as_int(b.w);
+            }
+            node = PTB_NODE_NONE;
+        } else {
+            const float4* np = bvh.node + 4 * (size_t)node;
+            float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            float t_l = slab_test(n0, n1, o, inv);
+            float t_r = slab_test(n2, n3, o, inv);
+            int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
+            bool hit_l = (t_l != -1.0f && t_l < h.t);
+            bool hit_r = (t_r != -1.0f && t_r < h.t);
+            if (hit_l && hit_r) {
+                bool left_first = t_l < t_r;
+                stack[(sp++) * stride] = left_first ? right : left;
+                node = left_first ? left : right;
+            } else if (hit_l) node = left;
+            else if (hit_r) node = right;
+            else node = PTB_NODE_NONE;
+        }
+        if (sp >= PTB_EXT_STACK) break;   // :106 -- the reference gives up here; so do we
+    }
+    return h;
+}
+
+// Any hit (TraceShadowRayKernel's visibility test, src/kernels/ray_cast.cu:136-191).  The
+// reference walks stacklessly over escape indices; the SET of nodes whose box passes
+// `t_box != -1 && tmax > t_box` does not depend on the order, so a stack walk finds an occluder
+// iff the reference does.  Returns 1 occluded, 0 visible, -1 stack overflow.
+template <int STACK>
+__device__ __forceinline__ int trace_any(const BvhDev& bvh, Vec3 o, Vec3 d, float tmax, int* stack, int stride) {
+    Vec3 inv(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    const float t_limit = __fsub_rn(tmax, PTB_EPSILON);
+    int sp = 0;
+    float t_root = slab_test(bvh.root_min, bvh.root_max, o, inv);
+    int node = (t_root != -1.0f && tmax > t_root) ? 0 : PTB_NODE_NONE;
+    while (node != PTB_NODE_NONE || sp > 0) {
+        if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
+        if (node < 0) {
+            const float4* tp = bvh.tri + 3 * (size_t)(~node);
+            float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            float u, v;
+            float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, u, v);
+            if (t > PTB_EPSILON && t < t_limit) return 1;
+            node = PTB_NODE_NONE;
+        } else {
+            const float4* np = bvh.node + 4 * (size_t)node;
+            float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            float t_l = slab_test(n0, n1, o, inv);
+            float t_r = slab_test(n2, n3, o, inv);
+            int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
+            bool hit_l = (t_l != -1.0f && tmax > t_l);
+            bool hit_r = (t_r != -1.0f && tmax > t_r);
+            if (hit_l && hit_r) {
+                if (sp >= STACK) return -1;
+                bool left_first = t_l <= t_r;
+                stack[(sp++) * stride] = left_first ? right : left;
+                node = left_first ? left : right;
+            } else if (hit_l) node = left;
+            else if (hit_r) node = right;
+            else node = PTB_NODE_NONE;
+        }
+    }
+    return 0;
+}
+
+}  // namespace ptb

@@ -1,0 +1,59 @@
+// render.cuh -- per-frame device state of the wavefront core and the stage launchers.
+// Replaces WavefrontPathTracerState's queue / counter members (src/wavefront_internal.h:10-92)
+// and the stage wrappers of src/kernels/{ray_gen,ray_cast,logic,shading}.h.
+#pragma once
+#include "common.cuh"
+
+namespace ptb {
+
+// Counter rows: row b holds the queue lengths of bounce b.  Nothing is reset inside a frame:
+// Shade(b) appends to row b+1, so the host never reads a counter back
+// (the reference does 6 blocking D2H reads + 6 memsets per bounce, src/pathtrace_wavefront.cu:286-343).
+enum { CTR_WORK_EXT = 6, CTR_WORK_SHADOW = 7 };   // work-fetch cursors of the persistent RayCast kernels
+
+struct FrameDev {
+    PathPool pool;
+    ShadowQueueDev shadow;
+    int* q_ext;
+    int* q_mat[4];            // PBR, DIFFUSE, REFLECT, REFRACT
+    int* ctr;                 // [(trace_depth + 1) * CTR_STRIDE]
+    unsigned long long* ray_totals;   // [2] extension / shadow rays since the last stats reset
+    int* iteration;           // 1-based sample index of the frame being rendered; advanced by frame_end
+    int* error_flag;          // set by a kernel on traversal-stack overflow
+    float* direct;            // 3 floats per owned pixel (d_direct_image, src/wavefront_internal.h:26)
+    float* indirect;          // (d_indirect_image, :27)
+    MeshDev mesh;
+    LightDev lights;
+    BvhDev bvh;
+    const ptb_material* materials;
+    TexturesDev tex;
+    CameraDev cam;
+    TileMap tile;
+    int trace_depth;
+    int num_paths;            // == tile.owned_pixels
+};
+
+struct LaunchCfg {
+    int num_sms;
+    int shadow_deep;          // 1: tree deeper than the shared-memory shadow stack -> local-memory variant
+};
+
+// Each returns the number of kernels it enqueued (for ptb_stats.kernel_launches).
+int launch_clear_accumulators(const FrameDev& f, cudaStream_t s);
+int launch_raygen(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);   // iteration is read from *f.iteration
+int launch_set_iteration(const FrameDev& f, int iteration, cudaStream_t s);
+int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);          // extension + shadow
+// Extension rays only, with a caller-provided (zeroed) work cursor: used to time the kernel alone.
+int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s);
+int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
+int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
+int launch_frame_end(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);                   // ray statistics
+int launch_resolve(const FrameDev& f, void* dst, int format, int iteration, cudaStream_t s);
+
+// Batched RayCast on caller rays (ptb_trace_closest / ptb_trace_occluded): device arrays.
+int launch_trace_batch_closest(const BvhDev& bvh, const float4* ori, const float4* dir, int n, int* hit, float* t, float* u,
+                               float* v, int* work, const LaunchCfg& c, cudaStream_t s);
+int launch_trace_batch_occluded(const BvhDev& bvh, const float4* ori_tmax, const float4* dir, int n, int* occluded, int* work,
+                                int* error_flag, const LaunchCfg& c, cudaStream_t s);
+
+}  // namespace ptb

@@ -1,0 +1,395 @@
+// stages.cu -- RayGen, Logic, Shading and resolve kernels of the wavefront core.
+// Reference: src/kernels/ray_gen.cu:15-79, src/kernels/logic.cu:31-192, src/kernels/shading.cu:23-259,
+// src/common/cuda_utilities.h:233-326, src/pathtrace_wavefront.cu:47-116.
+//
+// Differences from the reference that do not change a single sample:
+//   * queue lengths stay on the device (counter rows, render.cuh); every kernel is launched with a
+//     fixed grid and strides over `count` read from device memory, so a whole frame is one CUDA graph;
+//   * Logic walks the extension queue of the bounce instead of all P slots (the live slots of a
+//     bounce are exactly the paths that were traced, src/common/cuda_utilities.h:253-275);
+//   * the four material kernels are ONE launch: each material queue is cut into 32-path chunks so
+//     a warp always shades a single material type (type-uniform control flow, no divergence
+//     between models);
+//   * queue appends are warp-aggregated at a converged point (one atomic per warp per queue);
+//   * each path owns its pixel, so emission / environment adds are plain read-modify-writes.
+#include "bsdf.cuh"
+#include "render.cuh"
+
+namespace ptb {
+
+static constexpr int kThreads = 128;
+
+__device__ __forceinline__ Vec3 cam_v3(const float* p) { return Vec3(p[0], p[1], p[2]); }
+
+// ---- frame begin / RayGen ----------------------------------------------------------------------
+__global__ void k_clear(float* a, float* b, size_t n) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    size_t stride = gridDim.x * (size_t)blockDim.x;
+    for (; i < n; i += stride) { a[i] = 0.0f; b[i] = 0.0f; }
+}
+
+__global__ void __launch_bounds__(kThreads) k_raygen(FrameDev f) {
+    const int iter = *f.iteration;
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    // counter rows: everything zero except the first extension queue, which holds every path
+    int nctr = (f.trace_depth + 1) * CTR_STRIDE;
+    if (slot < nctr) f.ctr[slot] = (slot == CTR_EXT) ? f.num_paths : 0;
+    if (slot >= f.num_paths) return;
+    int pixel_idx = f.tile.global_pixel(slot);
+    int x = pixel_idx % f.cam.res_x;
+    int y = pixel_idx / f.cam.res_x;
+    // wang_hash((pixel_idx * 19990303) + iter * 719393) in wrapping int arithmetic, :41
+    uint32_t seed = wang_hash((uint32_t)pixel_idx * 19990303u + (uint32_t)iter * 719393u);
+    if (seed == 0) seed = 1;
+    seed = wang_hash(seed);
+    float jx = (float)seed / 4294967296.0f - 0.5f;
+    seed = wang_hash(seed);
+    float jy = (float)seed / 4294967296.0f - 0.5f;
+    Vec3 view = cam_v3(f.cam.view), right = cam_v3(f.cam.right), up = cam_v3(f.cam.up);
+    Vec3 dir = normalize3(view
+        + right * f.cam.pixel_length[0] * ((float)x + jx - (float)f.cam.res_x * 0.5f)
+        - up * f.cam.pixel_length[1] * ((float)y + jy - (float)f.cam.res_y * 0.5f));
+    f.pool.ray_ori[slot] = make_float4(f.cam.pos[0], f.cam.pos[1], f.cam.pos[2], 0.0f);
+    f.pool.ray_dir_dist[slot] = make_float4(dir.x, dir.y, dir.z, FLT_MAX);
+    f.pool.hit_geom_id[slot] = -1;
+    f.pool.material_id[slot] = -1;
+    f.pool.throughput_pdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+    f.pool.remaining_bounces[slot] = f.trace_depth;
+    f.pool.rng_state[slot] = seed;
+    f.q_ext[slot] = slot;
+}
+
+// ---- surface interpolation (GetSurfaceProperties, src/common/cuda_utilities.h:279-326) ---------
+__device__ __forceinline__ void surface_properties(const FrameDev& f, int prim, float u, float v, const Mat& mat, Vec3& N, float& uvx, float& uvy) {
+    int4 im = __ldg(&f.mesh.indices_matid[prim]);
+    float w = 1.0f - u - v;
+    float2 uv0 = __ldg(&f.mesh.uv[im.x]), uv1 = __ldg(&f.mesh.uv[im.y]), uv2 = __ldg(&f.mesh.uv[im.z]);
+    uvx = w * uv0.x + u * uv1.x + v * uv2.x;
+    uvy = w * uv0.y + u * uv1.y + v * uv2.y;
+    Vec3 n0 = make_v3(__ldg(&f.mesh.nor[im.x])), n1 = make_v3(__ldg(&f.mesh.nor[im.y])), n2 = make_v3(__ldg(&f.mesh.nor[im.z]));
+    Vec3 Ns = normalize3(w * n0 + u * n1 + v * n2);
+    if (mat.normal_tex < 0) { N = Ns; return; }
+    Vec3 t0 = make_v3(__ldg(&f.mesh.tangent[im.x])), t1 = make_v3(__ldg(&f.mesh.tangent[im.y])), t2 = make_v3(__ldg(&f.mesh.tangent[im.z]));
+    Vec3 Ti = w * t0 + u * t1 + v * t2;
+    Vec3 B = normalize3(cross3(Ns, Ti));
+    Vec3 T = cross3(B, Ns);
+    float4 s = tex2D<float4>(__ldg(&f.tex.handles[mat.normal_tex]), uvx, uvy);
+    Vec3 m(s.x * 2.0f - 1.0f, s.y * 2.0f - 1.0f, s.z * 2.0f - 1.0f);
+    // glm::mat3(T, B, N) * m = T*m.x + B*m.y + N*m.z (type_mat3x3.inl:487-493)
+    N = normalize3(Vec3(T.x * m.x + B.x * m.y + Ns.x * m.z, T.y * m.x + B.y * m.y + Ns.y * m.z, T.z * m.x + B.z * m.y + Ns.z * m.z));
+}
+
+__device__ __forceinline__ Vec3 pow3(Vec3 c, float e) { return Vec3(powf(c.x, e), powf(c.y, e), powf(c.z, e)); }
+
+// warp-aggregated append at a converged point: returns the slot for lanes with `want`
+__device__ __forceinline__ int warp_append(bool want, int* counter) {
+    unsigned int mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0) return -1;
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(mask) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return want ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
+}
+
+// ---- Logic (PathLogicKernel, src/kernels/logic.cu:31-192) --------------------------------------
+__global__ void __launch_bounds__(kThreads) k_logic(FrameDev f, int bounce) {
+    int* ctr = f.ctr + bounce * CTR_STRIDE;
+    const int count = ctr[CTR_EXT];
+    const int stride = gridDim.x * blockDim.x;
+    const int rounds = (count + stride - 1) / stride;
+    for (int r = 0; r < rounds; r++) {
+        int i = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        int queue = -1;
+        int idx = -1;
+        if (i < count) {
+            idx = __ldg(&f.q_ext[i]);
+            int hit = f.pool.hit_geom_id[idx];
+            int remaining = f.pool.remaining_bounces[idx];
+            float4 tp = f.pool.throughput_pdf[idx];
+            Vec3 throughput(tp.x, tp.y, tp.z);
+            float last_pdf = tp.w;
+            bool first = (remaining == f.trace_depth);
+            float* pix = f.indirect + 3 * (size_t)idx;
+            if (hit == -1) {
+                if (f.tex.env_tex_id >= 0) {
+                    float4 dd = f.pool.ray_dir_dist[idx];
+                    Vec3 dir = normalize3(Vec3(dd.x, dd.y, dd.z));
+                    float phi = atan2f(dir.z, dir.x);
+                    if (phi < 0) phi += PTB_TWO_PI;
+                    float theta = acosf(clampf(dir.y, -1.0f, 1.0f));
+                    float eu = phi * PTB_INV_TWO_PI;
+                    float ev = theta * PTB_INV_PI;
+                    float4 e4 = tex2D<float4>(__ldg(&f.tex.handles[f.tex.env_tex_id]), eu, ev);
+                    Vec3 env(e4.x, e4.y, e4.z);
+                    float mis = 1.0f;
+                    if (!first) {
+                        float pdf_bsdf = last_pdf;
+                        float pdf_env = tex2D<float>(__ldg(&f.tex.handles[f.tex.pdf_map_id]), eu, ev);
+                        if (pdf_bsdf > 1e10f) mis = 1.0f;
+                        else mis = (pdf_bsdf * pdf_bsdf) / (pdf_bsdf * pdf_bsdf + pdf_env * pdf_env + PTB_EPSILON);
+                    }
+                    Vec3 add = throughput * env * mis;
+                    pix[0] += add.x; pix[1] += add.y; pix[2] += add.z;
+                }
+                f.pool.remaining_bounces[idx] = -1;
+            } else {
+                int mat_id = f.pool.material_id[idx];
+                Mat m = load_material(f.materials, mat_id);
+                if (m.emittance > 0.0f) {
+                    float4 huv = f.pool.hit_uv[idx];
+                    Vec3 N; float uvx, uvy;
+                    surface_properties(f, hit, huv.x, huv.y, m, N, uvx, uvy);
+                    float4 dd = f.pool.ray_dir_dist[idx];
+                    Vec3 wo = -Vec3(dd.x, dd.y, dd.z);
+                    float mis = 1.0f;
+                    if (!first && f.lights.num_lights > 0) {
+                        bool prev_specular = (last_pdf > (PTB_PDF_DIRAC_DELTA * 0.9f));
+                        if (!prev_specular) {
+                            float dist = dd.w;
+                            float cos_light = fmaxf(dot3(N, wo), 0.0f);
+                            if (cos_light > PTB_EPSILON) {
+                                float pdf_area = 1.0f / f.lights.total_area;
+                                float pdf_sa = pdf_area * (dist * dist) / cos_light;
+                                mis = power_heuristic(last_pdf, pdf_sa);
+                            } else mis = 0.0f;
+                        }
+                    }
+                    Vec3 add = throughput * m.basecolor * m.emittance * mis;
+                    pix[0] += add.x; pix[1] += add.y; pix[2] += add.z;
+                    f.pool.remaining_bounces[idx] = -1;
+                } else {
+                    queue = m.type;
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            int pos = warp_append(queue == q, &ctr[CTR_PBR + q]);
+            if (pos >= 0) f.q_mat[q][pos] = idx;
+        }
+    }
+}
+
+// ---- Shading (src/kernels/shading.cu:23-259 + UpdatePathState, cuda_utilities.h:233-277) --------
+struct ShadeOut {
+    bool push_ext;
+    bool push_shadow;
+    float4 sh_ori_tmax, sh_dir, sh_rad;
+};
+
+template <int TYPE>
+__device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut& out) {
+    float4 dd = f.pool.ray_dir_dist[idx];
+    float4 oo = f.pool.ray_ori[idx];
+    float4 tp = f.pool.throughput_pdf[idx];
+    float4 huv = f.pool.hit_uv[idx];
+    int prim = f.pool.hit_geom_id[idx];
+    int mat_id = f.pool.material_id[idx];
+    Mat m = load_material(f.materials, mat_id);
+    Vec3 N; float uvx, uvy;
+    surface_properties(f, prim, huv.x, huv.y, m, N, uvx, uvy);
+    if (TYPE == MAT_PBR || TYPE == MAT_DIFFUSE) {
+        if (m.diffuse_tex >= 0) {
+            float4 tc = tex2D<float4>(__ldg(&f.tex.handles[m.diffuse_tex]), uvx, uvy);
+            m.basecolor = m.basecolor * pow3(Vec3(tc.x, tc.y, tc.z), 2.2f);
+        }
+    }
+    if (TYPE == MAT_PBR) {
+        if (m.mr_tex >= 0) {
+            float4 rm = tex2D<float4>(__ldg(&f.tex.handles[m.mr_tex]), uvx, uvy);
+            m.roughness *= rm.y;
+            m.metallic *= rm.z;
+        }
+    }
+    Vec3 dirv(dd.x, dd.y, dd.z);
+    Vec3 P = Vec3(oo.x, oo.y, oo.z) + dirv * dd.w;
+    Vec3 wo = -dirv;
+    Vec3 Ng = make_v3(__ldg(&f.mesh.nor_geom[prim]));
+    if (TYPE != MAT_REFRACT) { if (dot3(Ng, wo) < 0.0f) Ng = -Ng; }
+    uint32_t seed = f.pool.rng_state[idx];
+    Vec3 throughput(tp.x, tp.y, tp.z);
+
+    // ---- next-event estimation (ComputeNextEventEstimation, shading.cu:23-84).  The reference
+    // passes the seed BY VALUE, so light and BSDF sampling share random numbers; so do we.
+    if ((TYPE == MAT_PBR || TYPE == MAT_DIFFUSE) && f.lights.num_lights != 0) {
+        uint32_t nee_seed = seed;
+        Vec3 lp, ln; float pdf_area; int light_tri;
+        sample_light(f.mesh, f.lights, nee_seed, lp, ln, pdf_area, light_tri);
+        Vec3 wi = normalize3(lp - P);
+        float dist = length3(lp - P);
+        float dist_sq = glm_max(0.000001f, dist * dist);
+        float cos_surf = fmaxf(dot3(N, wi), 0.0f);
+        float cos_light = fmaxf(dot3(ln, -wi), 0.0f);
+        if (!(dot3(Ng, wi) <= 0.0f)) {
+            if (cos_surf > 0.0f && cos_light > 0.0f && pdf_area > 0.0f) {
+                int lmat_id = __ldg(&f.mesh.indices_matid[light_tri]).w;
+                Mat lm = load_material(f.materials, lmat_id);
+                Vec3 Le = lm.basecolor * lm.emittance;
+                Vec3 fr = eval_bsdf(wo, wi, N, m);
+                float pdf = pdf_bsdf(wo, wi, N, m);
+                if (length3(fr) > 0.0f) {
+                    float pdf_sa = pdf_area * dist_sq / cos_light;
+                    float weight = power_heuristic(pdf_sa, pdf);
+                    Vec3 L = throughput * Le * fr * (cos_surf * cos_light) / dist_sq * weight / pdf_area;
+                    if (length3(L) > 0.0f) {
+                        out.push_shadow = true;
+                        out.sh_ori_tmax = make_float4(P.x + Ng.x * PTB_EPSILON, P.y + Ng.y * PTB_EPSILON, P.z + Ng.z * PTB_EPSILON, dist);
+                        out.sh_dir = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                        out.sh_rad = make_float4(L.x, L.y, L.z, 0.0f);
+                    }
+                }
+            }
+        }
+    }
+
+    Vec3 next_dir(0.0f);
+    float next_pdf = 0.0f;
+    Vec3 att;
+    if (TYPE == MAT_PBR) att = sample_pbr(wo, next_dir, next_pdf, N, m, seed);
+    else if (TYPE == MAT_DIFFUSE) att = sample_diffuse(next_dir, next_pdf, N, m, seed);
+    else if (TYPE == MAT_REFLECT) att = sample_mirror(wo, next_dir, next_pdf, N, m);
+    else att = sample_dielectric(wo, next_dir, next_pdf, N, m, seed);
+
+    // ---- UpdatePathState
+    if (next_pdf > 0.0f && length3(att) > 0.0f) {
+        throughput = throughput * att;
+        Vec3 bias_n = Ng;
+        bool alive = true;
+        if (TYPE == MAT_REFRACT) {
+            bool exiting = dot3(next_dir, Ng) > 0.0f;
+            bias_n = exiting ? Ng : -Ng;
+        } else if (dot3(next_dir, Ng) <= 0.0f) {
+            alive = false;
+        }
+        if (alive) {
+            f.pool.throughput_pdf[idx] = make_float4(throughput.x, throughput.y, throughput.z, next_pdf);
+            f.pool.ray_ori[idx] = make_float4(P.x + bias_n.x * PTB_EPSILON, P.y + bias_n.y * PTB_EPSILON, P.z + bias_n.z * PTB_EPSILON, 0.0f);
+            f.pool.ray_dir_dist[idx] = make_float4(next_dir.x, next_dir.y, next_dir.z, FLT_MAX);
+            f.pool.remaining_bounces[idx] -= 1;
+            out.push_ext = true;
+        } else {
+            f.pool.remaining_bounces[idx] = -1;
+        }
+    } else {
+        f.pool.remaining_bounces[idx] = -1;
+    }
+    f.pool.rng_state[idx] = seed;
+}
+
+__global__ void __launch_bounds__(kThreads) k_shade(FrameDev f, int bounce) {
+    const int* ctr = f.ctr + bounce * CTR_STRIDE;
+    int* next = f.ctr + (bounce + 1) * CTR_STRIDE;
+    // chunk table: queue q owns chunks [c0[q], c0[q+1]) of 32 paths each
+    int n[4], c0[5];
+    c0[0] = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) { n[q] = ctr[CTR_PBR + q]; c0[q + 1] = c0[q] + ((n[q] + 31) >> 5); }
+    const int lane = threadIdx.x & 31;
+    const int warps_total = (gridDim.x * blockDim.x) >> 5;
+    const int warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    for (int chunk = warp_id; chunk < c0[4]; chunk += warps_total) {
+        int q = (chunk >= c0[3]) ? 3 : (chunk >= c0[2]) ? 2 : (chunk >= c0[1]) ? 1 : 0;
+        int i = ((chunk - c0[q]) << 5) + lane;
+        bool active = i < n[q];
+        ShadeOut out;
+        out.push_ext = false;
+        out.push_shadow = false;
+        int idx = -1;
+        if (active) {
+            idx = __ldg(&f.q_mat[q][i]);
+            if (q == MAT_PBR) shade_path<MAT_PBR>(f, idx, out);
+            else if (q == MAT_DIFFUSE) shade_path<MAT_DIFFUSE>(f, idx, out);
+            else if (q == MAT_REFLECT) shade_path<MAT_REFLECT>(f, idx, out);
+            else shade_path<MAT_REFRACT>(f, idx, out);
+        }
+        int sp = warp_append(out.push_shadow, &next[CTR_SHADOW]);
+        if (sp >= 0) {
+            f.shadow.ray_ori_tmax[sp] = out.sh_ori_tmax;
+            f.shadow.ray_dir[sp] = out.sh_dir;
+            f.shadow.radiance[sp] = out.sh_rad;
+            f.shadow.slot[sp] = idx;
+        }
+        int ep = warp_append(out.push_ext, &next[CTR_EXT]);
+        if (ep >= 0) f.q_ext[ep] = idx;
+    }
+}
+
+// ---- frame end: ray statistics (MraysPerSec's numerator, src/pathtrace_wavefront.cu:305) --------
+__global__ void k_frame_end(FrameDev f) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        unsigned long long e = 0, s = 0;
+        for (int b = 0; b < f.trace_depth; b++) {
+            e += (unsigned long long)f.ctr[b * CTR_STRIDE + CTR_EXT];
+            s += (unsigned long long)f.ctr[b * CTR_STRIDE + CTR_SHADOW];
+        }
+        f.ray_totals[0] += e;
+        f.ray_totals[1] += s;
+        *f.iteration += 1;
+    }
+}
+
+// ---- resolve (SendImageToPBOKernel mode 0, src/pathtrace_wavefront.cu:66-80,112-115) -----------
+__global__ void __launch_bounds__(256) k_resolve(const float* __restrict__ direct, const float* __restrict__ indirect, int n,
+                                                 void* dst, int format, int iter) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Vec3 c(direct[3 * (size_t)i] + indirect[3 * (size_t)i], direct[3 * (size_t)i + 1] + indirect[3 * (size_t)i + 1],
+         direct[3 * (size_t)i + 2] + indirect[3 * (size_t)i + 2]);
+    if (format == PTB_IMG_SUM_RGB32F) {
+        float* o = (float*)dst + 3 * (size_t)i;
+        o[0] = c.x; o[1] = c.y; o[2] = c.z;
+        return;
+    }
+    c = c / (float)iter;
+    if (format == PTB_IMG_MEAN_RGB32F) {
+        float* o = (float*)dst + 3 * (size_t)i;
+        o[0] = c.x; o[1] = c.y; o[2] = c.z;
+        return;
+    }
+    c = pow3(c, 1.0f / 2.2f);
+    uchar4 px;
+    px.x = (unsigned char)min(max((int)(c.x * 255.0f), 0), 255);
+    px.y = (unsigned char)min(max((int)(c.y * 255.0f), 0), 255);
+    px.z = (unsigned char)min(max((int)(c.z * 255.0f), 0), 255);
+    px.w = 255;
+    ((uchar4*)dst)[i] = px;
+}
+
+// ---- launchers ---------------------------------------------------------------------------------
+static inline int stage_grid(const LaunchCfg& c) { return c.num_sms * 8; }
+
+int launch_clear_accumulators(const FrameDev& f, cudaStream_t s) {
+    size_t n = 3 * (size_t)f.num_paths;
+    k_clear<<<1184, 256, 0, s>>>(f.direct, f.indirect, n);
+    return 1;
+}
+__global__ void k_set_iteration(int* p, int v) { *p = v; }
+int launch_set_iteration(const FrameDev& f, int iteration, cudaStream_t s) {
+    k_set_iteration<<<1, 1, 0, s>>>(f.iteration, iteration);
+    return 1;
+}
+int launch_raygen(const FrameDev& f, const LaunchCfg&, cudaStream_t s) {
+    int work = max(f.num_paths, (f.trace_depth + 1) * CTR_STRIDE);
+    k_raygen<<<(work + kThreads - 1) / kThreads, kThreads, 0, s>>>(f);
+    return 1;
+}
+int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
+    k_logic<<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    return 1;
+}
+int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
+    k_shade<<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    return 1;
+}
+int launch_frame_end(const FrameDev& f, const LaunchCfg&, cudaStream_t s) {
+    k_frame_end<<<1, 32, 0, s>>>(f);
+    return 1;
+}
+int launch_resolve(const FrameDev& f, void* dst, int format, int iteration, cudaStream_t s) {
+    k_resolve<<<(f.num_paths + 255) / 256, 256, 0, s>>>(f.direct, f.indirect, f.num_paths, dst, format, iteration);
+    return 1;
+}
+
+}  // namespace ptb

@@ -1,0 +1,740 @@
+// renderer.cu -- the ptb_renderer half of the C ABI (include/ptb200.h): device upload, LBVH build,
+// per-frame CUDA graph, staged (parity) execution, read-backs.
+// Replaces pathtrace_wavefront::{PathtraceInit, Pathtrace, PathtraceFree} (reference
+// src/pathtrace_wavefront.cu:144-413) and WavefrontPathTracerState (src/wavefront_internal.cu).
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../cuda/lbvh.cuh"
+#include "../cuda/render.cuh"
+#include "errors.hpp"
+#include "scene.hpp"
+
+using namespace ptb;
+
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(PTB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct ptb_renderer {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    ptb_config cfg{};
+
+    // scene replica on the device
+    std::vector<void*> allocs;               // everything cudaMalloc'ed here (freed in ptb_free)
+    std::vector<cudaArray_t> arrays;
+    std::vector<cudaTextureObject_t> textures;
+    LbvhBuffers lbvh;
+    FrameDev frame{};
+    LaunchCfg launch{};
+    size_t device_bytes = 0;
+
+    // frame graph
+    cudaGraphExec_t graph_exec = nullptr;
+    int device_iteration = -1;               // value *frame.iteration will hold when the stream drains
+
+    // staged execution state
+    int stage_bounce = 0;                    // bounce the next TRACE / LOGIC / SHADE works on
+    int logic_bounce = 0;                    // bounce of the last LOGIC (material queue counters)
+
+    // scratch for batched tracing / timing
+    void* scratch = nullptr;
+    size_t scratch_bytes = 0;
+    int* cursors = nullptr;                  // kMaxTimed work cursors + 1 for batches
+    std::vector<int32_t> owned_pixels_cache;
+
+    // stats
+    uint64_t frames = 0, kernel_launches = 0;
+    float lbvh_build_ms = 0.0f;
+    int lbvh_max_depth = 0;
+    int launches_per_frame = 0;
+};
+
+static constexpr int kMaxTimed = 4096;
+
+template <typename T>
+static int dev_alloc(ptb_renderer* r, T*& p, size_t count) {
+    size_t bytes = (count ? count : 1) * sizeof(T);
+    void* q = nullptr;
+    CU(cudaMalloc(&q, bytes));
+    r->allocs.push_back(q);
+    r->device_bytes += bytes;
+    p = (T*)q;
+    return PTB_OK;
+}
+
+template <typename T>
+static int dev_upload(ptb_renderer* r, T*& p, const void* src, size_t count) {
+    int rc = dev_alloc(r, p, count);
+    if (rc) return rc;
+    if (count) CU(cudaMemcpyAsync((void*)p, src, count * sizeof(T), cudaMemcpyHostToDevice, r->stream));
+    return PTB_OK;
+}
+
+static int ensure_scratch(ptb_renderer* r, size_t bytes) {
+    if (bytes <= r->scratch_bytes) return PTB_OK;
+    if (r->scratch) cudaFree(r->scratch);
+    r->scratch = nullptr;
+    r->scratch_bytes = 0;
+    CU(cudaMalloc(&r->scratch, bytes));
+    r->scratch_bytes = bytes;
+    return PTB_OK;
+}
+
+// Scene::createTexture (src/scene.h:94-145): wrap in X always, Y per texture, linear, normalised
+// coordinates, uchar4 -> normalised float.
+static int upload_texture(ptb_renderer* r, const HostTexture& t) {
+    cudaChannelFormatDesc desc;
+    size_t elem;
+    const void* src;
+    if (!t.is_float) { desc = cudaCreateChannelDesc<uchar4>(); elem = 4; src = t.rgba8.data(); }
+    else if (t.channels == 4) { desc = cudaCreateChannelDesc<float4>(); elem = 16; src = t.f32.data(); }
+    else { desc = cudaCreateChannelDesc<float>(); elem = 4; src = t.f32.data(); }
+    cudaArray_t arr = nullptr;
+    CU(cudaMallocArray(&arr, &desc, t.width, t.height));
+    r->arrays.push_back(arr);
+    CU(cudaMemcpy2DToArray(arr, 0, 0, src, t.width * elem, t.width * elem, t.height, cudaMemcpyHostToDevice));
+    cudaResourceDesc res;
+    memset(&res, 0, sizeof(res));
+    res.resType = cudaResourceTypeArray;
+    res.res.array.array = arr;
+    cudaTextureDesc td;
+    memset(&td, 0, sizeof(td));
+    td.readMode = t.is_float ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
+    td.addressMode[0] = cudaAddressModeWrap;
+    td.addressMode[1] = t.clamp_y ? cudaAddressModeClamp : cudaAddressModeWrap;
+    td.filterMode = cudaFilterModeLinear;
+    td.normalizedCoords = 1;
+    cudaTextureObject_t obj = 0;
+    CU(cudaCreateTextureObject(&obj, &res, &td, nullptr));
+    r->textures.push_back(obj);
+    r->device_bytes += (size_t)t.width * t.height * elem;
+    return PTB_OK;
+}
+
+static int owned_rows(const ptb_config& c, int height) {
+    if (c.world <= 1) return height;
+    int rows = 0;
+    for (int y = 0; y < height; y++)
+        if ((y / c.stripe_rows) % c.world == c.rank) rows++;
+    return rows;
+}
+
+static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
+    const FrameDev& f = r->frame;
+    int n = 0;
+    n += launch_raygen(f, r->launch, s);
+    for (int b = 0; b < f.trace_depth; b++) {
+        n += launch_trace(f, b, r->launch, s);
+        n += launch_logic(f, b, r->launch, s);
+        // Rays produced by the last Shade are never traced (loop bound src/pathtrace_wavefront.cu:281,
+        // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
+        if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
+    }
+    n += launch_frame_end(f, r->launch, s);
+    return n;
+}
+
+static int check_device_error(ptb_renderer* r) {
+    int flag = 0;
+    CU(cudaMemcpy(&flag, r->frame.error_flag, sizeof(int), cudaMemcpyDeviceToHost));
+    if (flag) {
+        cudaMemset(r->frame.error_flag, 0, sizeof(int));
+        return fail(PTB_ERR_UNSUPPORTED, "shadow-ray traversal stack overflow (LBVH deeper than the stack)");
+    }
+    return PTB_OK;
+}
+
+extern "C" {
+
+int ptb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+void ptb_config_default(ptb_config* cfg) {
+    if (!cfg) return;
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->device = 0;
+    cfg->trace_depth = 0;
+    cfg->rank = 0;
+    cfg->world = 1;
+    cfg->stripe_rows = 8;
+    cfg->use_graph = 1;
+}
+
+int ptb_free(ptb_renderer* r) {
+    if (!r) return PTB_OK;
+    cudaSetDevice(r->device);
+    if (r->stream) cudaStreamSynchronize(r->stream);
+    if (r->graph_exec) cudaGraphExecDestroy(r->graph_exec);
+    for (cudaTextureObject_t t : r->textures) cudaDestroyTextureObject(t);
+    for (cudaArray_t a : r->arrays) cudaFreeArray(a);
+    for (void* p : r->allocs) cudaFree(p);
+    if (r->scratch) cudaFree(r->scratch);
+    lbvh_free(r->lbvh);
+    if (r->own_stream && r->stream) cudaStreamDestroy(r->stream);
+    delete r;
+    return PTB_OK;
+}
+
+int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** out) {
+    if (!scene || !out) return fail(PTB_ERR_INVALID, "ptb_init: null argument");
+    *out = nullptr;
+    ptb_config cfg;
+    if (cfg_in) cfg = *cfg_in; else ptb_config_default(&cfg);
+    if (cfg.world < 1) cfg.world = 1;
+    if (cfg.stripe_rows < 1) cfg.stripe_rows = 8;
+    if (cfg.rank < 0 || cfg.rank >= cfg.world) return fail(PTB_ERR_INVALID, "ptb_init: rank outside [0, world)");
+    const int N = (int)scene->indices_matid.size();
+    const int V = (int)scene->pos.size();
+    if (N < 2) return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the LBVH needs at least 2 triangles (the reference's hierarchy is undefined below that)");
+    const int W = scene->camera.resolution[0], H = scene->camera.resolution[1];
+    if (W <= 0 || H <= 0) return fail(PTB_ERR_INVALID, "ptb_init: camera resolution not set");
+    int ndev = ptb_device_count();
+    if (ndev == 0) return fail(PTB_ERR_CUDA, "ptb_init: no CUDA device (this library has no CPU fallback)");
+    if (cfg.device < 0 || cfg.device >= ndev) return fail(PTB_ERR_INVALID, "ptb_init: device ordinal out of range");
+    CU(cudaSetDevice(cfg.device));
+
+    ptb_renderer* r = new ptb_renderer();
+    r->device = cfg.device;
+    r->cfg = cfg;
+#define TRY(x) do { int rc_ = (x); if (rc_) { ptb_free(r); return rc_; } } while (0)
+#define TRYCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { ptb_free(r); return fail(PTB_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); } } while (0)
+    TRYCU(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+    r->own_stream = true;
+    cudaDeviceProp prop;
+    TRYCU(cudaGetDeviceProperties(&prop, cfg.device));
+    r->launch.num_sms = prop.multiProcessorCount;
+
+    FrameDev& f = r->frame;
+    // ---- mesh, materials, lights (initSceneGeometry, src/wavefront_internal.cu:118-167)
+    float4 *pos, *nor, *tangent, *nor_geom; float2* uv; int4* im;
+    TRY(dev_upload(r, pos, scene->pos.data(), V));
+    TRY(dev_upload(r, nor, scene->nor.data(), V));
+    TRY(dev_upload(r, tangent, scene->tangent.data(), V));
+    TRY(dev_upload(r, uv, scene->uv.data(), V));
+    TRY(dev_upload(r, im, scene->indices_matid.data(), N));
+    TRY(dev_upload(r, nor_geom, scene->nor_geom.data(), N));
+    f.mesh.pos = pos; f.mesh.nor = nor; f.mesh.tangent = tangent; f.mesh.uv = uv;
+    f.mesh.indices_matid = im; f.mesh.nor_geom = nor_geom;
+    f.mesh.num_vertices = V; f.mesh.num_triangles = N;
+    ptb_material* mats;
+    TRY(dev_upload(r, mats, scene->materials.data(), scene->materials.size()));
+    f.materials = mats;
+    int* ltri; float* lcdf;
+    TRY(dev_upload(r, ltri, scene->light_tri_idx.data(), scene->light_tri_idx.size()));
+    TRY(dev_upload(r, lcdf, scene->light_cdf.data(), scene->light_cdf.size()));
+    f.lights.tri_idx = ltri; f.lights.cdf = lcdf;
+    f.lights.num_lights = (int)scene->light_tri_idx.size();
+    f.lights.total_area = scene->light_total_area;
+    // ---- textures
+    for (const HostTexture& t : scene->textures) TRY(upload_texture(r, t));
+    cudaTextureObject_t* dtex;
+    TRY(dev_upload(r, dtex, r->textures.data(), r->textures.size()));
+    f.tex.handles = dtex;
+    f.tex.env_tex_id = scene->env.env_tex_id;
+    f.tex.pdf_map_id = scene->env.pdf_map_id;
+
+    // ---- LBVH (initBVH, src/wavefront_internal.cu:180-193 -> BuildLBVH, src/bvh.cu:456-516)
+    {
+        int e = lbvh_alloc(r->lbvh, N);
+        if (e) { ptb_free(r); return fail(PTB_ERR_CUDA, std::string("lbvh_alloc: ") + cudaGetErrorString((cudaError_t)e)); }
+        r->device_bytes += r->lbvh.bytes;
+        cudaEvent_t e0, e1;
+        TRYCU(cudaEventCreate(&e0));
+        TRYCU(cudaEventCreate(&e1));
+        int launches = 0;
+        TRYCU(cudaEventRecord(e0, r->stream));
+        e = lbvh_build(r->lbvh, pos, im, r->stream, &launches);
+        TRYCU(cudaEventRecord(e1, r->stream));
+        TRYCU(cudaStreamSynchronize(r->stream));
+        if (e) { ptb_free(r); return fail(PTB_ERR_CUDA, std::string("lbvh_build: ") + cudaGetErrorString((cudaError_t)e)); }
+        TRYCU(cudaEventElapsedTime(&r->lbvh_build_ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        r->kernel_launches += launches;
+        TRYCU(cudaMemcpy(&r->lbvh_max_depth, r->lbvh.max_depth, sizeof(int), cudaMemcpyDeviceToHost));
+        float4 root[2];
+        TRYCU(cudaMemcpy(&root[0], r->lbvh.ref.aabb_min, sizeof(float4), cudaMemcpyDeviceToHost));
+        TRYCU(cudaMemcpy(&root[1], r->lbvh.ref.aabb_max, sizeof(float4), cudaMemcpyDeviceToHost));
+        f.bvh.node = r->lbvh.node;
+        f.bvh.tri = r->lbvh.tri;
+        f.bvh.root_min = root[0];
+        f.bvh.root_max = root[1];
+        f.bvh.num_triangles = N;
+        if (r->lbvh_max_depth > 256) { ptb_free(r); return fail(PTB_ERR_UNSUPPORTED, "ptb_init: LBVH deeper than 256 levels"); }
+        r->launch.shadow_deep = r->lbvh_max_depth > 64 ? 1 : 0;
+    }
+
+    // ---- path pool, queues, accumulators (initWavefrontQueues / initImageSystem,
+    //      src/wavefront_internal.cu:70-86,221-254) sized by the pixels this rank owns
+    f.tile.width = W; f.tile.height = H;
+    f.tile.rank = cfg.rank; f.tile.world = cfg.world; f.tile.stripe_rows = cfg.stripe_rows;
+    f.tile.owned_pixels = owned_rows(cfg, H) * W;
+    const size_t P = (size_t)f.tile.owned_pixels;
+    f.num_paths = (int)P;
+    f.trace_depth = cfg.trace_depth > 0 ? cfg.trace_depth : scene->trace_depth;
+    if (f.trace_depth < 1) f.trace_depth = 1;
+    TRY(dev_alloc(r, f.pool.ray_ori, P));
+    TRY(dev_alloc(r, f.pool.ray_dir_dist, P));
+    TRY(dev_alloc(r, f.pool.hit_uv, P));
+    TRY(dev_alloc(r, f.pool.throughput_pdf, P));
+    TRY(dev_alloc(r, f.pool.hit_geom_id, P));
+    TRY(dev_alloc(r, f.pool.material_id, P));
+    TRY(dev_alloc(r, f.pool.remaining_bounces, P));
+    TRY(dev_alloc(r, f.pool.rng_state, P));
+    TRY(dev_alloc(r, f.shadow.ray_ori_tmax, P));
+    TRY(dev_alloc(r, f.shadow.ray_dir, P));
+    TRY(dev_alloc(r, f.shadow.radiance, P));
+    TRY(dev_alloc(r, f.shadow.slot, P));
+    TRY(dev_alloc(r, f.q_ext, P));
+    for (int q = 0; q < 4; q++) TRY(dev_alloc(r, f.q_mat[q], P));
+    TRY(dev_alloc(r, f.ctr, (size_t)(f.trace_depth + 1) * CTR_STRIDE));
+    TRY(dev_alloc(r, f.ray_totals, 2));
+    TRY(dev_alloc(r, f.iteration, 1));
+    TRY(dev_alloc(r, f.error_flag, 1));
+    TRY(dev_alloc(r, f.direct, 3 * P));
+    TRY(dev_alloc(r, f.indirect, 3 * P));
+    TRY(dev_alloc(r, r->cursors, kMaxTimed + 1));
+    TRYCU(cudaMemsetAsync(f.ctr, 0, sizeof(int) * (f.trace_depth + 1) * CTR_STRIDE, r->stream));
+    TRYCU(cudaMemsetAsync(f.ray_totals, 0, 2 * sizeof(unsigned long long), r->stream));
+    TRYCU(cudaMemsetAsync(f.iteration, 0, sizeof(int), r->stream));
+    TRYCU(cudaMemsetAsync(f.error_flag, 0, sizeof(int), r->stream));
+    TRYCU(cudaMemsetAsync(f.direct, 0, 3 * P * sizeof(float), r->stream));
+    TRYCU(cudaMemsetAsync(f.indirect, 0, 3 * P * sizeof(float), r->stream));
+    // InitPathPoolKernel (src/pathtrace_wavefront.cu:183-190): every slot starts dead
+    TRYCU(cudaMemsetAsync(f.pool.remaining_bounces, 0xff, P * sizeof(int), r->stream));
+    TRYCU(cudaMemsetAsync(f.pool.hit_geom_id, 0xff, P * sizeof(int), r->stream));
+
+    // ---- camera
+    const ptb_camera& c = scene->camera;
+    f.cam.res_x = W; f.cam.res_y = H;
+    for (int i = 0; i < 3; i++) { f.cam.pos[i] = c.position[i]; f.cam.view[i] = c.view[i]; f.cam.up[i] = c.up[i]; f.cam.right[i] = c.right[i]; }
+    f.cam.pixel_length[0] = c.pixel_length[0];
+    f.cam.pixel_length[1] = c.pixel_length[1];
+
+    // ---- one CUDA graph per frame (the reference re-launches ~10 kernels per bounce with a
+    //      cudaDeviceSynchronize after each, src/common/cuda_utilities.cu:4)
+    if (cfg.use_graph) {
+        cudaGraph_t graph = nullptr;
+        TRYCU(cudaStreamSynchronize(r->stream));
+        TRYCU(cudaStreamBeginCapture(r->stream, cudaStreamCaptureModeThreadLocal));
+        r->launches_per_frame = enqueue_frame(r, r->stream);
+        cudaError_t ce = cudaStreamEndCapture(r->stream, &graph);
+        if (ce != cudaSuccess) { ptb_free(r); return fail(PTB_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(ce)); }
+        ce = cudaGraphInstantiate(&r->graph_exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ce != cudaSuccess) { r->graph_exec = nullptr; ptb_free(r); return fail(PTB_ERR_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(ce)); }
+    }
+    TRYCU(cudaStreamSynchronize(r->stream));
+    r->device_iteration = 0;
+#undef TRY
+#undef TRYCU
+    *out = r;
+    return PTB_OK;
+}
+
+}  // extern "C"
+
+// ===================================================================== rendering ================
+extern "C" {
+
+int ptb_set_stream(ptb_renderer* r, void* cuda_stream) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_set_stream: null renderer");
+    CU(cudaSetDevice(r->device));
+    CU(cudaStreamSynchronize(r->stream));
+    if (r->own_stream) cudaStreamDestroy(r->stream);
+    r->stream = (cudaStream_t)cuda_stream;
+    r->own_stream = false;
+    return PTB_OK;
+}
+
+int ptb_sync(ptb_renderer* r) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_sync: null renderer");
+    CU(cudaSetDevice(r->device));
+    CU(cudaStreamSynchronize(r->stream));
+    return check_device_error(r);
+}
+
+int ptb_render_many(ptb_renderer* r, int32_t first, int32_t count) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_render: null renderer");
+    if (first < 1 || count < 0) return fail(PTB_ERR_INVALID, "ptb_render: iteration is 1-based");
+    CU(cudaSetDevice(r->device));
+    for (int32_t it = first; it < first + count; it++) {
+        // iteration 1 restarts the accumulation (src/pathtrace_wavefront.cu:232-242)
+        if (it == 1) r->kernel_launches += launch_clear_accumulators(r->frame, r->stream);
+        if (r->device_iteration != it) r->kernel_launches += launch_set_iteration(r->frame, it, r->stream);
+        if (r->graph_exec) {
+            CU(cudaGraphLaunch(r->graph_exec, r->stream));
+            r->kernel_launches += r->launches_per_frame;
+        } else {
+            r->kernel_launches += enqueue_frame(r, r->stream);
+        }
+        r->device_iteration = it + 1;
+        r->frames++;
+    }
+    CU(cudaGetLastError());
+    return PTB_OK;
+}
+
+int ptb_render(ptb_renderer* r, int32_t iteration) { return ptb_render_many(r, iteration, 1); }
+
+int ptb_resolve(ptb_renderer* r, void* dst, int32_t format, int32_t iteration, int32_t dst_on_device) {
+    if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_resolve: null argument");
+    if (format < PTB_IMG_SUM_RGB32F || format > PTB_IMG_RGBA8) return fail(PTB_ERR_INVALID, "ptb_resolve: unknown format");
+    if (format != PTB_IMG_SUM_RGB32F && iteration < 1) return fail(PTB_ERR_INVALID, "ptb_resolve: iteration must be >= 1");
+    CU(cudaSetDevice(r->device));
+    const size_t P = (size_t)r->frame.num_paths;
+    const size_t bytes = P * (format == PTB_IMG_RGBA8 ? 4 : 12);
+    if (dst_on_device) {
+        r->kernel_launches += launch_resolve(r->frame, dst, format, iteration, r->stream);
+        CU(cudaGetLastError());
+        return PTB_OK;
+    }
+    int rc = ensure_scratch(r, bytes);
+    if (rc) return rc;
+    r->kernel_launches += launch_resolve(r->frame, r->scratch, format, iteration, r->stream);
+    CU(cudaMemcpyAsync(dst, r->scratch, bytes, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return check_device_error(r);
+}
+
+int ptb_get_accumulators(ptb_renderer* r, float* direct, float* indirect) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_get_accumulators: null renderer");
+    CU(cudaSetDevice(r->device));
+    CU(cudaStreamSynchronize(r->stream));
+    const size_t bytes = 3 * (size_t)r->frame.num_paths * sizeof(float);
+    if (direct) CU(cudaMemcpy(direct, r->frame.direct, bytes, cudaMemcpyDeviceToHost));
+    if (indirect) CU(cudaMemcpy(indirect, r->frame.indirect, bytes, cudaMemcpyDeviceToHost));
+    return check_device_error(r);
+}
+
+int ptb_get_tile_info(const ptb_renderer* r, ptb_tile_info* out) {
+    if (!r || !out) return fail(PTB_ERR_INVALID, "ptb_get_tile_info: null argument");
+    out->width = r->frame.tile.width;
+    out->height = r->frame.tile.height;
+    out->owned_pixels = r->frame.tile.owned_pixels;
+    out->rank = r->frame.tile.rank;
+    out->world = r->frame.tile.world;
+    out->stripe_rows = r->frame.tile.stripe_rows;
+    return PTB_OK;
+}
+
+int ptb_get_owned_pixels(const ptb_renderer* r, int32_t* dst, int32_t capacity) {
+    if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_owned_pixels: null argument");
+    int n = r->frame.tile.owned_pixels;
+    if (capacity < n) n = capacity;
+    for (int i = 0; i < n; i++) dst[i] = r->frame.tile.global_pixel(i);
+    return r->frame.tile.owned_pixels;
+}
+
+// ===================================================================== LBVH view ================
+int64_t ptb_get_lbvh(ptb_renderer* r, int which, void* dst, size_t bytes) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_get_lbvh: null renderer");
+    const size_t N = (size_t)r->lbvh.num_triangles;
+    const void* src = nullptr;
+    size_t size = 0;
+    switch (which) {
+        case PTB_LBVH_AABB_MIN: src = r->lbvh.ref.aabb_min; size = 2 * N * sizeof(float4); break;
+        case PTB_LBVH_AABB_MAX: src = r->lbvh.ref.aabb_max; size = 2 * N * sizeof(float4); break;
+        case PTB_LBVH_CENTROID: src = r->lbvh.ref.centroid; size = 2 * N * sizeof(float4); break;
+        case PTB_LBVH_PRIMITIVE_INDICES: src = r->lbvh.ref.primitive_indices; size = 2 * N * sizeof(int); break;
+        case PTB_LBVH_MORTON_CODES: src = r->lbvh.ref.morton_codes; size = N * sizeof(unsigned long long); break;
+        case PTB_LBVH_CHILD_NODES: src = r->lbvh.ref.child_nodes; size = (N - 1) * sizeof(int2); break;
+        case PTB_LBVH_PARENT: src = r->lbvh.ref.parent; size = 2 * N * sizeof(int); break;
+        case PTB_LBVH_ESCAPE_INDICES: src = r->lbvh.ref.escape_indices; size = 2 * N * sizeof(int); break;
+        case PTB_LBVH_WORLD_AABB: src = r->lbvh.ref.world_aabb; size = 2 * sizeof(float4); break;
+        default: return fail(PTB_ERR_INVALID, "ptb_get_lbvh: unknown array id");
+    }
+    if (dst && bytes) {
+        CU(cudaSetDevice(r->device));
+        CU(cudaStreamSynchronize(r->stream));
+        CU(cudaMemcpy(dst, src, bytes < size ? bytes : size, cudaMemcpyDeviceToHost));
+    }
+    return (int64_t)size;
+}
+
+int ptb_build_lbvh(int32_t device, const float* pos4, int32_t V, const int32_t* indices_matid4, int32_t N,
+                   uint64_t* morton_codes, int32_t* primitive_indices, int32_t* child_nodes, int32_t* parent,
+                   int32_t* escape_indices, float* aabb_min4, float* aabb_max4, float* world_aabb8, float* build_ms) {
+    if (!pos4 || !indices_matid4) return fail(PTB_ERR_INVALID, "ptb_build_lbvh: null input");
+    if (N < 2) return fail(PTB_ERR_UNSUPPORTED, "ptb_build_lbvh: needs at least 2 triangles");
+    if (V < 1) return fail(PTB_ERR_INVALID, "ptb_build_lbvh: no vertices");
+    for (int64_t i = 0; i < (int64_t)N; i++)
+        for (int k = 0; k < 3; k++)
+            if (indices_matid4[4 * i + k] < 0 || indices_matid4[4 * i + k] >= V) return fail(PTB_ERR_INVALID, "ptb_build_lbvh: vertex index out of range");
+    if (ptb_device_count() == 0) return fail(PTB_ERR_CUDA, "ptb_build_lbvh: no CUDA device (no CPU fallback)");
+    CU(cudaSetDevice(device));
+    float4* dpos = nullptr; int4* dim = nullptr;
+    LbvhBuffers b;
+    cudaStream_t s = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int rc = PTB_OK;
+    auto cleanup = [&]() {
+        if (dpos) cudaFree(dpos);
+        if (dim) cudaFree(dim);
+        lbvh_free(b);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+        if (s) cudaStreamDestroy(s);
+    };
+#define G(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { rc = fail(PTB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); cleanup(); return rc; } } while (0)
+    G(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    G(cudaEventCreate(&e0));
+    G(cudaEventCreate(&e1));
+    G(cudaMalloc((void**)&dpos, (size_t)V * sizeof(float4)));
+    G(cudaMalloc((void**)&dim, (size_t)N * sizeof(int4)));
+    G((cudaError_t)lbvh_alloc(b, N));
+    G(cudaMemcpyAsync(dpos, pos4, (size_t)V * sizeof(float4), cudaMemcpyHostToDevice, s));
+    G(cudaMemcpyAsync(dim, indices_matid4, (size_t)N * sizeof(int4), cudaMemcpyHostToDevice, s));
+    G(cudaEventRecord(e0, s));
+    G((cudaError_t)lbvh_build(b, dpos, dim, s, nullptr));
+    G(cudaEventRecord(e1, s));
+    G(cudaStreamSynchronize(s));
+    if (build_ms) G(cudaEventElapsedTime(build_ms, e0, e1));
+    const size_t n = (size_t)N;
+    if (morton_codes) G(cudaMemcpy(morton_codes, b.ref.morton_codes, n * 8, cudaMemcpyDeviceToHost));
+    if (primitive_indices) G(cudaMemcpy(primitive_indices, b.ref.primitive_indices, 2 * n * 4, cudaMemcpyDeviceToHost));
+    if (child_nodes) G(cudaMemcpy(child_nodes, b.ref.child_nodes, (n - 1) * 8, cudaMemcpyDeviceToHost));
+    if (parent) G(cudaMemcpy(parent, b.ref.parent, 2 * n * 4, cudaMemcpyDeviceToHost));
+    if (escape_indices) G(cudaMemcpy(escape_indices, b.ref.escape_indices, 2 * n * 4, cudaMemcpyDeviceToHost));
+    if (aabb_min4) G(cudaMemcpy(aabb_min4, b.ref.aabb_min, 2 * n * 16, cudaMemcpyDeviceToHost));
+    if (aabb_max4) G(cudaMemcpy(aabb_max4, b.ref.aabb_max, 2 * n * 16, cudaMemcpyDeviceToHost));
+    if (world_aabb8) G(cudaMemcpy(world_aabb8, b.ref.world_aabb, 32, cudaMemcpyDeviceToHost));
+#undef G
+    cleanup();
+    return PTB_OK;
+}
+
+// ===================================================================== batched RayCast ==========
+int ptb_trace_closest(ptb_renderer* r, const float* ori4, const float* dir4, int32_t n, int32_t* hit, float* t, float* u, float* v) {
+    if (!r || !ori4 || !dir4 || !hit || !t || !u || !v) return fail(PTB_ERR_INVALID, "ptb_trace_closest: null argument");
+    if (n < 0) return fail(PTB_ERR_INVALID, "ptb_trace_closest: negative count");
+    if (n == 0) return PTB_OK;
+    CU(cudaSetDevice(r->device));
+    const size_t N = (size_t)n;
+    int rc = ensure_scratch(r, N * (16 + 16 + 4 * 4));
+    if (rc) return rc;
+    char* base = (char*)r->scratch;
+    float4* dori = (float4*)base; float4* ddir = (float4*)(base + 16 * N);
+    int* dhit = (int*)(base + 32 * N); float* dt = (float*)(base + 36 * N); float* du = (float*)(base + 40 * N); float* dv = (float*)(base + 44 * N);
+    CU(cudaMemcpyAsync(dori, ori4, 16 * N, cudaMemcpyHostToDevice, r->stream));
+    CU(cudaMemcpyAsync(ddir, dir4, 16 * N, cudaMemcpyHostToDevice, r->stream));
+    r->kernel_launches += launch_trace_batch_closest(r->frame.bvh, dori, ddir, n, dhit, dt, du, dv, r->cursors + kMaxTimed, r->launch, r->stream);
+    CU(cudaMemcpyAsync(hit, dhit, 4 * N, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaMemcpyAsync(t, dt, 4 * N, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaMemcpyAsync(u, du, 4 * N, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaMemcpyAsync(v, dv, 4 * N, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return PTB_OK;
+}
+
+int ptb_trace_occluded(ptb_renderer* r, const float* ori_tmax4, const float* dir4, int32_t n, int32_t* occluded) {
+    if (!r || !ori_tmax4 || !dir4 || !occluded) return fail(PTB_ERR_INVALID, "ptb_trace_occluded: null argument");
+    if (n < 0) return fail(PTB_ERR_INVALID, "ptb_trace_occluded: negative count");
+    if (n == 0) return PTB_OK;
+    CU(cudaSetDevice(r->device));
+    const size_t N = (size_t)n;
+    int rc = ensure_scratch(r, N * (16 + 16 + 4));
+    if (rc) return rc;
+    char* base = (char*)r->scratch;
+    float4* dori = (float4*)base; float4* ddir = (float4*)(base + 16 * N); int* docc = (int*)(base + 32 * N);
+    CU(cudaMemcpyAsync(dori, ori_tmax4, 16 * N, cudaMemcpyHostToDevice, r->stream));
+    CU(cudaMemcpyAsync(ddir, dir4, 16 * N, cudaMemcpyHostToDevice, r->stream));
+    r->kernel_launches += launch_trace_batch_occluded(r->frame.bvh, dori, ddir, n, docc, r->cursors + kMaxTimed, r->frame.error_flag, r->launch, r->stream);
+    CU(cudaMemcpyAsync(occluded, docc, 4 * N, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return check_device_error(r);
+}
+
+}  // extern "C"
+
+// ===================================================================== staged frame =============
+extern "C" {
+
+int ptb_stage_run(ptb_renderer* r, int32_t stage, int32_t iteration) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_stage_run: null renderer");
+    CU(cudaSetDevice(r->device));
+    const FrameDev& f = r->frame;
+    switch (stage) {
+        case PTB_STAGE_RAYGEN:
+            if (iteration < 1) return fail(PTB_ERR_INVALID, "ptb_stage_run: iteration is 1-based");
+            if (iteration == 1) r->kernel_launches += launch_clear_accumulators(f, r->stream);
+            r->kernel_launches += launch_set_iteration(f, iteration, r->stream);
+            r->kernel_launches += launch_raygen(f, r->launch, r->stream);
+            r->device_iteration = iteration;   // frame_end is not run in staged mode
+            r->stage_bounce = 0;
+            r->logic_bounce = 0;
+            break;
+        case PTB_STAGE_TRACE:
+            if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
+            r->kernel_launches += launch_trace(f, r->stage_bounce, r->launch, r->stream);
+            break;
+        case PTB_STAGE_LOGIC:
+            if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
+            r->kernel_launches += launch_logic(f, r->stage_bounce, r->launch, r->stream);
+            r->logic_bounce = r->stage_bounce;
+            break;
+        case PTB_STAGE_SHADE:
+            if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
+            r->kernel_launches += launch_shade(f, r->stage_bounce, r->launch, r->stream);
+            r->stage_bounce++;
+            break;
+        default:
+            return fail(PTB_ERR_INVALID, "ptb_stage_run: unknown stage");
+    }
+    CU(cudaGetLastError());
+    return PTB_OK;
+}
+
+static int queue_counter(ptb_renderer* r, int which, int* count) {
+    int row, col;
+    switch (which) {
+        case PTB_Q_EXTENSION: row = r->stage_bounce; col = CTR_EXT; break;
+        case PTB_Q_SHADOW: row = r->stage_bounce; col = CTR_SHADOW; break;
+        case PTB_Q_PBR: case PTB_Q_DIFFUSE: case PTB_Q_REFLECTION: case PTB_Q_REFRACTION:
+            row = r->logic_bounce; col = CTR_PBR + (which - PTB_Q_PBR); break;
+        default: return fail(PTB_ERR_INVALID, "unknown queue id");
+    }
+    CU(cudaStreamSynchronize(r->stream));
+    CU(cudaMemcpy(count, r->frame.ctr + row * CTR_STRIDE + col, sizeof(int), cudaMemcpyDeviceToHost));
+    return PTB_OK;
+}
+
+int ptb_get_queue_count(ptb_renderer* r, int32_t which, int32_t* count) {
+    if (!r || !count) return fail(PTB_ERR_INVALID, "ptb_get_queue_count: null argument");
+    CU(cudaSetDevice(r->device));
+    return queue_counter(r, which, count);
+}
+
+int ptb_get_queue(ptb_renderer* r, int32_t which, int32_t* dst, int32_t capacity) {
+    if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_queue: null argument");
+    CU(cudaSetDevice(r->device));
+    int n = 0;
+    int rc = queue_counter(r, which, &n);
+    if (rc) return rc;
+    int m = n < capacity ? n : capacity;
+    const int* src;
+    if (which == PTB_Q_EXTENSION) src = r->frame.q_ext;
+    else if (which == PTB_Q_SHADOW) src = r->frame.shadow.slot;
+    else src = r->frame.q_mat[which - PTB_Q_PBR];
+    if (m > 0) CU(cudaMemcpy(dst, src, (size_t)m * sizeof(int), cudaMemcpyDeviceToHost));
+    if (r->frame.tile.world > 1)
+        for (int i = 0; i < m; i++) dst[i] = r->frame.tile.global_pixel(dst[i]);
+    return n;
+}
+
+int ptb_get_shadow_queue(ptb_renderer* r, float* ori_tmax4, float* dir4, float* radiance4, int32_t* pixel_idx, int32_t capacity) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_get_shadow_queue: null renderer");
+    CU(cudaSetDevice(r->device));
+    int n = 0;
+    int rc = queue_counter(r, PTB_Q_SHADOW, &n);
+    if (rc) return rc;
+    size_t m = (size_t)(n < capacity ? n : capacity);
+    if (m > 0) {
+        if (ori_tmax4) CU(cudaMemcpy(ori_tmax4, r->frame.shadow.ray_ori_tmax, m * 16, cudaMemcpyDeviceToHost));
+        if (dir4) CU(cudaMemcpy(dir4, r->frame.shadow.ray_dir, m * 16, cudaMemcpyDeviceToHost));
+        if (radiance4) CU(cudaMemcpy(radiance4, r->frame.shadow.radiance, m * 16, cudaMemcpyDeviceToHost));
+        if (pixel_idx) {
+            CU(cudaMemcpy(pixel_idx, r->frame.shadow.slot, m * 4, cudaMemcpyDeviceToHost));
+            if (r->frame.tile.world > 1)
+                for (size_t i = 0; i < m; i++) pixel_idx[i] = r->frame.tile.global_pixel(pixel_idx[i]);
+        }
+    }
+    return n;
+}
+
+int ptb_get_path_field(ptb_renderer* r, int32_t field, void* dst, size_t bytes) {
+    if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_path_field: null argument");
+    CU(cudaSetDevice(r->device));
+    const void* src;
+    size_t elem;
+    switch (field) {
+        case PTB_PF_RAY_ORI: src = r->frame.pool.ray_ori; elem = 16; break;
+        case PTB_PF_RAY_DIR_DIST: src = r->frame.pool.ray_dir_dist; elem = 16; break;
+        case PTB_PF_HIT_UV: src = r->frame.pool.hit_uv; elem = 16; break;
+        case PTB_PF_THROUGHPUT_PDF: src = r->frame.pool.throughput_pdf; elem = 16; break;
+        case PTB_PF_HIT_GEOM_ID: src = r->frame.pool.hit_geom_id; elem = 4; break;
+        case PTB_PF_MATERIAL_ID: src = r->frame.pool.material_id; elem = 4; break;
+        case PTB_PF_REMAINING_BOUNCES: src = r->frame.pool.remaining_bounces; elem = 4; break;
+        case PTB_PF_RNG_STATE: src = r->frame.pool.rng_state; elem = 4; break;
+        default: return fail(PTB_ERR_INVALID, "ptb_get_path_field: unknown field");
+    }
+    const TileMap& tm = r->frame.tile;
+    const size_t full = (size_t)tm.width * tm.height * elem;
+    if (bytes < full) return fail(PTB_ERR_INVALID, "ptb_get_path_field: buffer smaller than width*height elements");
+    CU(cudaStreamSynchronize(r->stream));
+    if (tm.world <= 1) {
+        CU(cudaMemcpy(dst, src, full, cudaMemcpyDeviceToHost));
+        return PTB_OK;
+    }
+    std::vector<char> tmp((size_t)tm.owned_pixels * elem);
+    CU(cudaMemcpy(tmp.data(), src, tmp.size(), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < tm.owned_pixels; i++)
+        memcpy((char*)dst + (size_t)tm.global_pixel(i) * elem, tmp.data() + (size_t)i * elem, elem);
+    return PTB_OK;
+}
+
+// ===================================================================== stats ====================
+int ptb_get_stats(ptb_renderer* r, ptb_stats* out) {
+    if (!r || !out) return fail(PTB_ERR_INVALID, "ptb_get_stats: null argument");
+    CU(cudaSetDevice(r->device));
+    CU(cudaStreamSynchronize(r->stream));
+    unsigned long long rays[2] = {0, 0};
+    CU(cudaMemcpy(rays, r->frame.ray_totals, sizeof(rays), cudaMemcpyDeviceToHost));
+    memset(out, 0, sizeof(*out));
+    out->extension_rays = rays[0];
+    out->shadow_rays = rays[1];
+    out->frames = r->frames;
+    out->kernel_launches = r->kernel_launches;
+    out->lbvh_build_ms = r->lbvh_build_ms;
+    out->lbvh_max_depth = r->lbvh_max_depth;
+    out->num_triangles = r->lbvh.num_triangles;
+    return check_device_error(r);
+}
+
+int ptb_stats_reset(ptb_renderer* r) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_stats_reset: null renderer");
+    CU(cudaSetDevice(r->device));
+    CU(cudaMemsetAsync(r->frame.ray_totals, 0, 2 * sizeof(unsigned long long), r->stream));
+    r->frames = 0;
+    r->kernel_launches = 0;
+    return PTB_OK;
+}
+
+int ptb_time_raycast(ptb_renderer* r, int32_t count, float* avg_ms, int32_t* rays) {
+    if (!r || !avg_ms) return fail(PTB_ERR_INVALID, "ptb_time_raycast: null argument");
+    if (count < 1 || count > kMaxTimed) return fail(PTB_ERR_INVALID, "ptb_time_raycast: count must be in [1, 4096]");
+    if (r->stage_bounce >= r->frame.trace_depth) return fail(PTB_ERR_STATE, "ptb_time_raycast: no live extension queue");
+    CU(cudaSetDevice(r->device));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    CU(cudaMemsetAsync(r->cursors, 0, sizeof(int) * count, r->stream));
+    CU(cudaEventRecord(e0, r->stream));
+    for (int i = 0; i < count; i++) r->kernel_launches += launch_trace_extension_only(r->frame, r->stage_bounce, r->cursors + i, r->launch, r->stream);
+    CU(cudaEventRecord(e1, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    float ms = 0.0f;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *avg_ms = ms / (float)count;
+    if (rays) {
+        int n = 0;
+        CU(cudaMemcpy(&n, r->frame.ctr + r->stage_bounce * CTR_STRIDE + CTR_EXT, sizeof(int), cudaMemcpyDeviceToHost));
+        *rays = n;
+    }
+    return PTB_OK;
+}
+
+}  // extern "C"

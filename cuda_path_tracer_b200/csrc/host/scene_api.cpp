@@ -1,0 +1,154 @@
+// scene_api.cpp -- the ptb_scene_* half of the C ABI (include/ptb200.h).  Pure host code.
+// Replaces `class Scene` (reference src/scene.h:51-92, src/scene.cpp:45-631).
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+#include "errors.hpp"
+#include "scene.hpp"
+
+using namespace ptb;
+
+namespace ptb {
+thread_local std::string g_last_error;
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+}  // namespace ptb
+
+extern "C" {
+
+int ptb_abi_version(void) { return PTB_ABI_VERSION; }
+const char* ptb_last_error(void) { return g_last_error.c_str(); }
+
+int ptb_scene_load(const char* json_path, ptb_scene** out) {
+    if (!json_path || !out) return fail(PTB_ERR_INVALID, "ptb_scene_load: null argument");
+    *out = nullptr;
+    std::string path(json_path);
+    // Only .json scenes are accepted (src/scene.cpp:48-55)
+    if (path.size() < 5 || path.substr(path.size() - 5) != ".json") return fail(PTB_ERR_INVALID, "ptb_scene_load: not a .json scene: " + path);
+    ptb_scene* s = new ptb_scene();
+    try {
+        load_scene_json(path, *s);
+    } catch (const std::exception& e) {
+        delete s;
+        std::string msg = e.what();
+        int code = msg.find("open") != std::string::npos ? PTB_ERR_IO : PTB_ERR_PARSE;
+        return fail(code, "ptb_scene_load: " + msg);
+    }
+    *out = s;
+    return PTB_OK;
+}
+
+int ptb_scene_from_arrays(const float* pos, const float* nor, const float* uv, const float* tangent, int32_t num_vertices,
+                          const int32_t* indices, const int32_t* material_ids, int32_t num_triangles,
+                          const ptb_material* materials, int32_t num_materials, const ptb_camera* camera,
+                          int32_t trace_depth, ptb_scene** out) {
+    if (!pos || !nor || !indices || !material_ids || !materials || !camera || !out)
+        return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: null argument");
+    if (num_vertices <= 0 || num_triangles <= 0 || num_materials <= 0) return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: empty scene");
+    *out = nullptr;
+    for (int64_t i = 0; i < 3 * (int64_t)num_triangles; i++)
+        if (indices[i] < 0 || indices[i] >= num_vertices) return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: vertex index out of range");
+    for (int32_t i = 0; i < num_triangles; i++)
+        if (material_ids[i] < 0 || material_ids[i] >= num_materials) return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: material id out of range");
+    ptb_scene* s = new ptb_scene();
+    s->pos.resize(num_vertices); s->nor.resize(num_vertices); s->tangent.resize(num_vertices); s->uv.resize(num_vertices);
+    for (int32_t i = 0; i < num_vertices; i++) {
+        s->pos[i] = f4{pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], 1.0f};
+        // upload-time normalisation, src/wavefront_internal.cu:136-144
+        V3 n = normalize(V3(nor[3 * i], nor[3 * i + 1], nor[3 * i + 2]));
+        s->nor[i] = f4{n.x, n.y, n.z, 0.0f};
+        V3 t = tangent ? normalize(V3(tangent[3 * i], tangent[3 * i + 1], tangent[3 * i + 2])) : normalize(V3(0, 0, 0));
+        s->tangent[i] = f4{t.x, t.y, t.z, 0.0f};
+        s->uv[i] = uv ? f2{uv[2 * i], uv[2 * i + 1]} : f2{0.0f, 0.0f};
+    }
+    s->indices_matid.resize(num_triangles); s->nor_geom.resize(num_triangles);
+    for (int32_t i = 0; i < num_triangles; i++) {
+        int a = indices[3 * i], b = indices[3 * i + 1], c = indices[3 * i + 2];
+        s->indices_matid[i] = i4{a, b, c, material_ids[i]};
+        V3 p0(pos[3 * a], pos[3 * a + 1], pos[3 * a + 2]), p1(pos[3 * b], pos[3 * b + 1], pos[3 * b + 2]), p2(pos[3 * c], pos[3 * c + 1], pos[3 * c + 2]);
+        V3 ng = normalize(cross(p1 - p0, p2 - p0));   // src/scene.cpp:518-519
+        s->nor_geom[i] = f4{ng.x, ng.y, ng.z, 0.0f};
+    }
+    s->materials.assign(materials, materials + num_materials);
+    s->camera = *camera;
+    s->trace_depth = trace_depth > 0 ? trace_depth : 8;
+    build_light_cdf(*s);
+    *out = s;
+    return PTB_OK;
+}
+
+int ptb_scene_set_environment(ptb_scene* s, const float* rgb, int32_t width, int32_t height) {
+    if (!s || !rgb || width <= 0 || height <= 0) return fail(PTB_ERR_INVALID, "ptb_scene_set_environment: bad argument");
+    if (s->env.width > 0) return fail(PTB_ERR_STATE, "ptb_scene_set_environment: environment already set");
+    build_env_alias_table(*s, rgb, width, height);
+    return PTB_OK;
+}
+
+int ptb_scene_set_camera(ptb_scene* s, const int32_t resolution[2], float fovy_deg, const float eye[3], const float look_at[3],
+                         const float up[3], int32_t trace_depth) {
+    if (!s || !resolution || !eye || !look_at || !up) return fail(PTB_ERR_INVALID, "ptb_scene_set_camera: null argument");
+    if (resolution[0] <= 0 || resolution[1] <= 0) return fail(PTB_ERR_INVALID, "ptb_scene_set_camera: bad resolution");
+    s->camera.resolution[0] = resolution[0]; s->camera.resolution[1] = resolution[1];
+    for (int i = 0; i < 3; i++) { s->camera.position[i] = eye[i]; s->camera.look_at[i] = look_at[i]; s->camera.up[i] = up[i]; }
+    derive_camera(s->camera, fovy_deg);
+    if (trace_depth > 0) s->trace_depth = trace_depth;
+    return PTB_OK;
+}
+
+void ptb_scene_free(ptb_scene* s) { delete s; }
+
+int ptb_scene_get_info(const ptb_scene* s, ptb_scene_info* out) {
+    if (!s || !out) return fail(PTB_ERR_INVALID, "ptb_scene_get_info: null argument");
+    memset(out, 0, sizeof(*out));
+    out->num_vertices = (int32_t)s->pos.size();
+    out->num_triangles = (int32_t)s->indices_matid.size();
+    out->num_materials = (int32_t)s->materials.size();
+    out->num_lights = (int32_t)s->light_tri_idx.size();
+    out->num_textures = (int32_t)s->textures.size();
+    out->width = s->camera.resolution[0];
+    out->height = s->camera.resolution[1];
+    out->trace_depth = s->trace_depth;
+    out->iterations = s->iterations;
+    out->env_width = s->env.width;
+    out->env_height = s->env.height;
+    out->env_tex_id = s->env.env_tex_id;
+    out->pdf_map_id = s->env.pdf_map_id;
+    out->light_total_area = s->light_total_area;
+    return PTB_OK;
+}
+
+int ptb_scene_get_camera(const ptb_scene* s, ptb_camera* out) {
+    if (!s || !out) return fail(PTB_ERR_INVALID, "ptb_scene_get_camera: null argument");
+    *out = s->camera;
+    return PTB_OK;
+}
+
+int64_t ptb_scene_get_array(const ptb_scene* s, int which, void* dst, size_t bytes) {
+    if (!s) return fail(PTB_ERR_INVALID, "ptb_scene_get_array: null scene");
+    const void* src = nullptr;
+    size_t size = 0;
+#define VIEW(v) do { src = (v).data(); size = (v).size() * sizeof((v)[0]); } while (0)
+    switch (which) {
+        case PTB_SA_POS: VIEW(s->pos); break;
+        case PTB_SA_NOR: VIEW(s->nor); break;
+        case PTB_SA_TANGENT: VIEW(s->tangent); break;
+        case PTB_SA_UV: VIEW(s->uv); break;
+        case PTB_SA_INDICES_MATID: VIEW(s->indices_matid); break;
+        case PTB_SA_NOR_GEOM: VIEW(s->nor_geom); break;
+        case PTB_SA_MATERIALS: VIEW(s->materials); break;
+        case PTB_SA_LIGHT_TRI_IDX: VIEW(s->light_tri_idx); break;
+        case PTB_SA_LIGHT_CDF: VIEW(s->light_cdf); break;
+        case PTB_SA_ENV_PROBS: VIEW(s->env.probs); break;
+        case PTB_SA_ENV_ALIASES: VIEW(s->env.aliases); break;
+        case PTB_SA_ENV_PDF: VIEW(s->env.pdf_map); break;
+        default: return fail(PTB_ERR_INVALID, "ptb_scene_get_array: unknown array id");
+    }
+#undef VIEW
+    if (dst && bytes) memcpy(dst, src, bytes < size ? bytes : size);
+    return (int64_t)size;
+}
+
+}  // extern "C"
