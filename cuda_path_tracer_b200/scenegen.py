@@ -1,0 +1,324 @@
+"""Procedural scenes in the reference's own formats (scene.json + OBJ [+ MTL, textures, .hdr]).
+
+The reference ships no assets (its scenes/ directory is git-ignored) and this box has no network,
+so BASELINE.json's configs are rendered on deterministic procedural stand-ins with the same
+triangle counts and material mix.  Every generator is a pure function of its arguments: the
+reference build (oracle/_ref/refdump) and this library both load the files written here.
+Every mesh carries `vn` records: a vertex without a normal becomes NaN at upload in the
+reference (src/wavefront_internal.cu:139).
+"""
+import json
+import os
+import struct
+
+import numpy as np
+
+
+# ------------------------------------------------------------------------------------ primitives
+def grid(origin, du, dv, nu, nv, normal, bump=0.0, seed=0):
+    """(nu x nv) quads spanning origin + s*du + t*dv, displaced along `normal` by smooth noise."""
+    origin, du, dv, normal = (np.asarray(a, np.float64) for a in (origin, du, dv, normal))
+    s, t = np.meshgrid(np.linspace(0, 1, nu + 1), np.linspace(0, 1, nv + 1), indexing="ij")
+    p = origin + s[..., None] * du + t[..., None] * dv
+    n = np.broadcast_to(normal, p.shape).copy()
+    if bump > 0:
+        rng = np.random.RandomState(seed)
+        ph = rng.uniform(0, 2 * np.pi, 6)
+        fr = rng.uniform(3.0, 11.0, 6)
+        h = bump * (np.sin(fr[0] * s * 2 * np.pi + ph[0]) * np.cos(fr[1] * t * 2 * np.pi + ph[1])
+                    + 0.5 * np.sin(fr[2] * (s + t) * 2 * np.pi + ph[2]) + 0.25 * np.cos(fr[3] * (s - t) * 2 * np.pi + ph[3]))
+        p = p + h[..., None] * normal
+        dhs = np.gradient(h, axis=0) * nu
+        dht = np.gradient(h, axis=1) * nv
+        ts = du + dhs[..., None] * normal
+        tt = dv + dht[..., None] * normal
+        n = np.cross(ts, tt)
+        n /= np.linalg.norm(n, axis=-1, keepdims=True)
+        n *= np.sign((n * normal).sum(-1, keepdims=True))
+    idx = np.arange((nu + 1) * (nv + 1)).reshape(nu + 1, nv + 1)
+    a, b, c, d = idx[:-1, :-1], idx[1:, :-1], idx[1:, 1:], idx[:-1, 1:]
+    flip = np.dot(np.cross(du, dv), normal) < 0
+    t1 = np.stack([a, b, c], -1) if not flip else np.stack([a, c, b], -1)
+    t2 = np.stack([a, c, d], -1) if not flip else np.stack([a, d, c], -1)
+    tris = np.concatenate([t1.reshape(-1, 3), t2.reshape(-1, 3)])
+    uv = np.stack([s, t], -1).reshape(-1, 2)
+    return p.reshape(-1, 3), n.reshape(-1, 3), uv, tris
+
+
+def sphere(center, radius, stacks, slices):
+    """UV sphere, 2*slices*(stacks-1) triangles."""
+    center = np.asarray(center, np.float64)
+    th = np.linspace(0, np.pi, stacks + 1)[1:-1]
+    ph = np.linspace(0, 2 * np.pi, slices, endpoint=False)
+    T, Ph = np.meshgrid(th, ph, indexing="ij")
+    n = np.stack([np.sin(T) * np.cos(Ph), np.cos(T), np.sin(T) * np.sin(Ph)], -1).reshape(-1, 3)
+    n = np.concatenate([[[0, 1, 0]], n, [[0, -1, 0]]])
+    p = center + radius * n
+    uv = np.concatenate([[[0.5, 0.0]], np.stack([Ph / (2 * np.pi), T / np.pi], -1).reshape(-1, 2), [[0.5, 1.0]]])
+    tris = []
+    ring = lambda r: 1 + r * slices + np.arange(slices)
+    r0 = ring(0)
+    tris.append(np.stack([np.zeros(slices, int), np.roll(r0, -1), r0], -1))
+    for r in range(stacks - 2):
+        a, b = ring(r), ring(r + 1)
+        a2, b2 = np.roll(a, -1), np.roll(b, -1)
+        tris.append(np.stack([a, a2, b2], -1))
+        tris.append(np.stack([a, b2, b], -1))
+    rl = ring(stacks - 2)
+    last = 1 + (stacks - 1) * slices
+    tris.append(np.stack([rl, np.roll(rl, -1), np.full(slices, last)], -1))
+    return p, n, uv, np.concatenate(tris)
+
+
+def box(lo, hi):
+    """Axis-aligned box, 12 triangles, flat normals, outward."""
+    lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+    P, N, U, T = [], [], [], []
+    for axis in range(3):
+        for sign in (-1, 1):
+            u, v = (axis + 1) % 3, (axis + 2) % 3
+            c = np.zeros((4, 3))
+            c[:, axis] = hi[axis] if sign > 0 else lo[axis]
+            c[:, u] = [lo[u], hi[u], hi[u], lo[u]]
+            c[:, v] = [lo[v], lo[v], hi[v], hi[v]]
+            n = np.zeros(3)
+            n[axis] = sign
+            b = 4 * len(T) // 2
+            P.append(c)
+            N.append(np.tile(n, (4, 1)))
+            U.append(np.array([[0, 0], [1, 0], [1, 1], [0, 1]], float))
+            T.append(np.array([[b, b + 1, b + 2], [b, b + 2, b + 3]]) if sign > 0 else np.array([[b, b + 2, b + 1], [b, b + 3, b + 2]]))
+    return np.concatenate(P), np.concatenate(N), np.concatenate(U), np.concatenate(T)
+
+
+def ribbon(start, step, up, normal, count):
+    """A strip of exactly `count` triangles (filler to reach an exact triangle budget)."""
+    start, step, up, normal = (np.asarray(a, np.float64) for a in (start, step, up, normal))
+    k = count + 2
+    i = np.arange(k)
+    p = start + (i // 2)[:, None] * step + (i % 2)[:, None] * up
+    n = np.tile(normal / np.linalg.norm(normal), (k, 1))
+    uv = np.stack([(i // 2) / max(1, k // 2), (i % 2).astype(float)], -1)
+    t = np.stack([i[:-2], i[1:-1], i[2:]], -1)
+    odd = (np.arange(count) % 2) == 1
+    t[odd] = t[odd][:, [1, 0, 2]]
+    if np.dot(np.cross(step, up), normal) < 0:
+        t = t[:, [0, 2, 1]]
+    return p, n, uv, t
+
+
+def merge(parts):
+    P, N, U, T, base = [], [], [], [], 0
+    for p, n, u, t in parts:
+        P.append(p); N.append(n); U.append(u); T.append(t + base)
+        base += len(p)
+    return np.concatenate(P), np.concatenate(N), np.concatenate(U), np.concatenate(T)
+
+
+# ------------------------------------------------------------------------------------ writers
+def write_obj(path, p, n, uv, tris, mtllib=None, usemtl=None, with_uv=False):
+    """One OBJ: v / vn [/ vt] per vertex, `f a/a/a` or `f a//a`.  usemtl: None or per-triangle names."""
+    lines = []
+    if mtllib:
+        lines.append(f"mtllib {mtllib}")
+    lines += ["v %.6f %.6f %.6f" % tuple(r) for r in p]
+    lines += ["vn %.6f %.6f %.6f" % tuple(r) for r in n]
+    if with_uv:
+        lines += ["vt %.6f %.6f" % tuple(r) for r in uv]
+    cur = None
+    t1 = tris + 1
+    for k, (a, b, c) in enumerate(t1):
+        if usemtl is not None and usemtl[k] != cur:
+            cur = usemtl[k]
+            lines.append(f"usemtl {cur}")
+        if with_uv:
+            lines.append(f"f {a}/{a}/{a} {b}/{b}/{b} {c}/{c}/{c}")
+        else:
+            lines.append(f"f {a}//{a} {b}//{b} {c}//{c}")
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+
+
+def write_bmp(path, rgb):
+    """24-bit uncompressed BMP (bottom-up), readable by stb_image and by csrc/host/image_io.cpp."""
+    h, w, _ = rgb.shape
+    row = (3 * w + 3) & ~3
+    data = np.zeros((h, row), np.uint8)
+    data[:, :3 * w] = rgb[::-1, :, ::-1].reshape(h, 3 * w)
+    with open(path, "wb") as f:
+        f.write(b"BM" + struct.pack("<IHHI", 54 + row * h, 0, 0, 54))
+        f.write(struct.pack("<IiiHHIIiiII", 40, w, h, 1, 24, 0, row * h, 2835, 2835, 0, 0))
+        f.write(data.tobytes())
+
+
+def write_hdr(path, rgb):
+    """Radiance .hdr, flat (non-RLE) RGBE scanlines."""
+    h, w, _ = rgb.shape
+    m = rgb.max(-1)
+    e = np.where(m > 1e-32, np.floor(np.log2(np.maximum(m, 1e-38))) + 1, 0)
+    scale = np.where(m > 1e-32, 256.0 / np.exp2(e), 0.0)
+    out = np.zeros((h, w, 4), np.uint8)
+    out[..., :3] = np.clip(rgb * scale[..., None], 0, 255).astype(np.uint8)
+    out[..., 3] = np.where(m > 1e-32, e + 128, 0).astype(np.uint8)
+    with open(path, "wb") as f:
+        f.write(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n" + f"-Y {h} +X {w}\n".encode())
+        f.write(out.tobytes())
+
+
+def write_scene(path, camera, materials, objects, env=None):
+    doc = {"Camera": camera, "Materials": materials, "Objects": objects}
+    if env:
+        doc["Environment Texture"] = {"FILE": env}
+    with open(path, "w") as f:
+        json.dump(doc, f, indent=1)
+
+
+def _obj_entry(file, material=None):
+    e = {"TRANS": [0, 0, 0], "ROTAT": [0, 0, 0], "SCALE": [1, 1, 1], "FILE": file}
+    if material:
+        e["MATERIAL"] = material
+    return e
+
+
+def _mat(color, kind="DIFFUSE", metallic=0.0, roughness=0.5, emittance=0.0, ior=1.0):
+    return {"basecolor": list(color), "metallic": metallic, "roughness": roughness, "emittance": emittance, "ior": ior, "Type": kind}
+
+
+# ------------------------------------------------------------------------------------ config 1
+def cornell(out_dir, res=(800, 800), depth=8):
+    """Cornell-style box in the reference's schema: Lambertian walls + one emissive quad + two boxes."""
+    os.makedirs(out_dir, exist_ok=True)
+    mats = {"white": _mat([0.73, 0.73, 0.73]), "red": _mat([0.65, 0.05, 0.05]), "green": _mat([0.12, 0.45, 0.15]),
+            "light": _mat([1.0, 0.9, 0.7], emittance=12.0)}
+    objs = []
+
+    def add(name, part, material):
+        write_obj(os.path.join(out_dir, name + ".obj"), *part)
+        objs.append(_obj_entry(os.path.join(out_dir, name + ".obj"), material))
+
+    add("floor", grid([-1, 0, -1], [2, 0, 0], [0, 0, 2], 2, 2, [0, 1, 0]), "white")
+    add("ceiling", grid([-1, 2, -1], [2, 0, 0], [0, 0, 2], 2, 2, [0, -1, 0]), "white")
+    add("back", grid([-1, 0, -1], [2, 0, 0], [0, 2, 0], 2, 2, [0, 0, 1]), "white")
+    add("left", grid([-1, 0, -1], [0, 0, 2], [0, 2, 0], 2, 2, [1, 0, 0]), "red")
+    add("right", grid([1, 0, -1], [0, 0, 2], [0, 2, 0], 2, 2, [-1, 0, 0]), "green")
+    add("lamp", grid([-0.3, 1.995, -0.3], [0.6, 0, 0], [0, 0, 0.6], 1, 1, [0, -1, 0]), "light")
+    add("tall", box([-0.65, 0.0, -0.6], [-0.1, 1.2, -0.05]), "white")
+    add("short", box([0.1, 0.0, 0.0], [0.65, 0.6, 0.55]), "white")
+    cam = {"RES": list(res), "FOVY": 39.0, "ITERATIONS": 16, "DEPTH": depth, "FILE": "cornell",
+           "EYE": [0.0, 1.0, 3.9], "LOOKAT": [0.0, 1.0, 0.0], "UP": [0.0, 1.0, 0.0]}
+    path = os.path.join(out_dir, "scene.json")
+    write_scene(path, cam, mats, objs)
+    return path
+
+
+# ------------------------------------------------------------------------------------ config 2
+FIREPLACE_MIX = {"MicrofacetPBR": 24421, "DIFFUSE": 107572, "SPECULAR_REFLECTION": 10, "SPECULAR_REFRACTION": 11170}
+
+
+def fireplace(out_dir, res=(1920, 1080), depth=8, scale=1.0):
+    """143,173-triangle room with the material mix the reference README quotes for Fireplace Room
+    (README.md:34): PBR 24,421 / diffuse 107,572 / mirror 10 / dielectric 11,170.  `scale` < 1
+    shrinks every tessellation (for quick tests); the mix is exact only at scale == 1."""
+    os.makedirs(out_dir, exist_ok=True)
+    rng = np.random.RandomState(20240607)
+    q = lambda v: max(2, int(round(v * scale)))
+    mats = {
+        "wall": _mat([0.72, 0.68, 0.62]), "floor": _mat([0.45, 0.33, 0.25]), "brick": _mat([0.55, 0.22, 0.16]),
+        "ball": _mat([0.25, 0.35, 0.65]), "trim": _mat([0.8, 0.8, 0.75]),
+        "lamp": _mat([1.0, 0.85, 0.6], emittance=18.0),
+        "gold": _mat([1.0, 0.77, 0.34], "MicrofacetPBR", metallic=1.0, roughness=0.25),
+        "plastic": _mat([0.8, 0.1, 0.1], "MicrofacetPBR", metallic=0.0, roughness=0.35),
+        "steel": _mat([0.6, 0.62, 0.65], "MicrofacetPBR", metallic=0.9, roughness=0.5),
+        "ceramic": _mat([0.9, 0.9, 0.85], "MicrofacetPBR", metallic=0.0, roughness=0.15),
+        "glass": _mat([0.95, 0.98, 1.0], "SPECULAR_REFRACTION", ior=1.5),
+        "mirror": _mat([0.95, 0.95, 0.95], "SPECULAR_REFLECTION", metallic=1.0, roughness=0.0),
+    }
+    objs, counts = [], {k: 0 for k in FIREPLACE_MIX}
+
+    def add(name, part, material):
+        write_obj(os.path.join(out_dir, name + ".obj"), *part)
+        objs.append(_obj_entry(os.path.join(out_dir, name + ".obj"), material))
+        counts[mats[material]["Type"]] += len(part[3])
+
+    X, Y, Z = 5.0, 5.0, 5.0
+    g = q(100)
+    add("floor", grid([-X, 0, -Z], [2 * X, 0, 0], [0, 0, 2 * Z], g, g, [0, 1, 0], 0.03, 1), "floor")
+    add("ceiling", grid([-X, Y, -Z], [2 * X, 0, 0], [0, 0, 2 * Z], g, g, [0, -1, 0], 0.03, 2), "wall")
+    h = q(50)
+    add("wall_back", grid([-X, 0, -Z], [2 * X, 0, 0], [0, Y, 0], g, h, [0, 0, 1], 0.04, 3), "wall")
+    add("wall_front", grid([-X, 0, Z], [2 * X, 0, 0], [0, Y, 0], g, h, [0, 0, -1], 0.04, 4), "wall")
+    add("wall_left", grid([-X, 0, -Z], [0, 0, 2 * Z], [0, Y, 0], g, h, [1, 0, 0], 0.04, 5), "wall")
+    add("wall_right", grid([X, 0, -Z], [0, 0, 2 * Z], [0, Y, 0], g, h, [-1, 0, 0], 0.04, 6), "wall")
+    bricks = []
+    for _ in range(q(200)):   # a fireplace-ish pile of bricks along the back wall
+        c = np.array([rng.uniform(-2.0, 2.0), rng.uniform(0.05, 2.2), rng.uniform(-4.7, -3.9)])
+        s = np.array([rng.uniform(0.08, 0.2), rng.uniform(0.04, 0.09), rng.uniform(0.06, 0.12)])
+        bricks.append(box(c - s, c + s))
+    add("bricks", merge(bricks), "brick")
+    balls = [sphere([rng.uniform(-3.5, 3.5), 0.45, rng.uniform(-2.5, 2.5)], 0.42, q(40), q(60)) for _ in range(5)]
+    add("balls", merge(balls), "ball")
+    for k, m in enumerate(["gold", "plastic", "steel", "ceramic"]):
+        add(f"pbr_{m}", sphere([-3.0 + 2.0 * k, 1.0 + 0.25 * (k % 2), -1.0 - 0.6 * (k % 2)], 0.7, q(48), q(64)), m)
+    glass = [sphere([-1.2, 0.62, 1.4], 0.6, q(59), q(48)), sphere([1.4, 0.52, 1.9], 0.5, q(59), q(48))]
+    add("glass", merge(glass), "glass")
+    lamps = [grid([cx - 0.5, Y - 0.06, cz - 0.5], [1.0, 0, 0], [0, 0, 1.0], 1, 1, [0, -1, 0]) for cx in (-2.2, 2.2) for cz in (-2.2, 2.2)]
+    add("lamps", merge(lamps), "lamp")
+    add("mirror", ribbon([X - 0.08, 1.0, -1.5], [0, 0, 0.6], [0, 2.0, 0], [-1, 0, 0], 10), "mirror")
+    if scale == 1.0:   # fillers: bring each material class to the README's exact count
+        add("trim_pbr", ribbon([-X + 0.05, 0.4, -4.0], [0, 0, 0.04], [0, 0.12, 0], [1, 0, 0], FIREPLACE_MIX["MicrofacetPBR"] - counts["MicrofacetPBR"]), "steel")
+        add("trim_glass", ribbon([-2.0, 2.6, -Z + 0.06], [0.1, 0, 0], [0, 0.3, 0], [0, 0, 1], FIREPLACE_MIX["SPECULAR_REFRACTION"] - counts["SPECULAR_REFRACTION"]), "glass")
+        add("trim_diffuse", ribbon([-X + 0.1, 0.08, Z - 0.06], [0.011, 0, 0], [0, 0.1, 0], [0, 0, -1], FIREPLACE_MIX["DIFFUSE"] - counts["DIFFUSE"]), "trim")
+        assert counts == FIREPLACE_MIX, counts
+    cam = {"RES": list(res), "FOVY": 55.0, "ITERATIONS": 16, "DEPTH": depth, "FILE": "fireplace",
+           "EYE": [0.3, 2.2, 4.6], "LOOKAT": [0.0, 1.4, -2.0], "UP": [0.0, 1.0, 0.0]}
+    path = os.path.join(out_dir, "scene.json")
+    write_scene(path, cam, mats, objs)
+    return path, sum(counts.values())
+
+
+# ------------------------------------------------------------------------------------ config 4
+def heightfield_arrays(num_triangles, seed=7, extent=40.0):
+    """Displaced height field + scattered micro-triangles as plain arrays (too large for OBJ text):
+    pos (V,3), nor (V,3), indices (N,3), material_ids (N,), all for Scene.from_arrays."""
+    n_field = int(num_triangles * 0.9)
+    g = int(np.sqrt(n_field / 2))
+    p, n, uv, t = grid([-extent, 0, -extent], [2 * extent, 0, 0], [0, 0, 2 * extent], g, g, [0, 1, 0], 1.5, seed)
+    rest = num_triangles - len(t)
+    rng = np.random.RandomState(seed)
+    c = np.stack([rng.uniform(-extent, extent, rest), rng.uniform(2.0, 12.0, rest), rng.uniform(-extent, extent, rest)], -1)
+    d1 = rng.normal(0, 0.08, (rest, 3))
+    d2 = rng.normal(0, 0.08, (rest, 3))
+    mp = np.stack([c, c + d1, c + d2], 1).reshape(-1, 3)
+    mn = np.cross(d1, d2)
+    mn /= np.maximum(np.linalg.norm(mn, axis=-1, keepdims=True), 1e-20)
+    mn = np.repeat(mn, 3, axis=0)
+    mt = np.arange(3 * rest).reshape(-1, 3) + len(p)
+    pos = np.concatenate([p, mp]).astype(np.float32)
+    nor = np.concatenate([n, mn]).astype(np.float32)
+    idx = np.concatenate([t, mt]).astype(np.int32)
+    mat = np.zeros(len(idx), np.int32)
+    mat[len(t):] = 1 + (np.arange(rest) % 3)
+    # a few large emissive triangles high above the field
+    lp = np.array([[-6, 30, -6], [6, 30, -6], [6, 30, 6], [-6, 30, 6]], np.float32)
+    ln = np.tile(np.array([[0, -1, 0]], np.float32), (4, 1))
+    base = len(pos)
+    pos = np.concatenate([pos, lp]); nor = np.concatenate([nor, ln])
+    idx[-2] = [base, base + 1, base + 2]; idx[-1] = [base, base + 2, base + 3]
+    mat[-2:] = 4
+    return pos, nor, idx, mat
+
+
+def stress_materials():
+    from .capi import MATERIAL_DTYPE
+    m = np.zeros(5, MATERIAL_DTYPE)
+    spec = [([0.55, 0.5, 0.42], 1, 0, 0.5, 0, 1), ([0.9, 0.6, 0.2], 0, 1.0, 0.3, 0, 1), ([0.95, 0.97, 1.0], 3, 0, 0, 0, 1.5),
+            ([0.2, 0.5, 0.8], 1, 0, 0.5, 0, 1), ([1.0, 0.95, 0.85], 1, 0, 0.5, 40.0, 1)]
+    for i, (c, ty, me, ro, em, ior) in enumerate(spec):
+        m[i]["basecolor"] = c; m[i]["type"] = ty; m[i]["metallic"] = me; m[i]["roughness"] = ro
+        m[i]["emittance"] = em; m[i]["ior"] = ior
+        m[i]["diffuse_tex_id"] = m[i]["normal_tex_id"] = m[i]["metallic_roughness_tex_id"] = -1
+    return m
+
+
+def stress_camera(res=(1920, 1080)):
+    return dict(resolution=res, fovy=50.0, eye=[0.0, 14.0, 38.0], look_at=[0.0, 2.0, 0.0], up=[0.0, 1.0, 0.0])

@@ -1,0 +1,274 @@
+"""Host-side mirror of the reference's render-path interface, over the C ABI.
+
+Reference interface (C++):            here:
+  Scene(filename)                      Scene(filename) / Scene.from_arrays(...)
+  pathtrace_wavefront::PathtraceInit   PathtraceInit(scene) -> module-level renderer (one per process,
+  pathtrace_wavefront::Pathtrace         like the reference's static pState) or Renderer(scene, ...) handles
+  pathtrace_wavefront::PathtraceFree   PathtraceFree()
+  BuildLBVH(LBVHData&, MeshData)       build_lbvh(pos4, indices_matid4)
+(reference: src/pathtrace_wavefront.h:6-12, src/scene.h:51-92, src/bvh.h:7.)
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import check, lib, ptr
+
+SA = dict(pos=(0, "<f4", 4), nor=(1, "<f4", 4), tangent=(2, "<f4", 4), uv=(3, "<f4", 2), indices_matid=(4, "<i4", 4),
+          nor_geom=(5, "<f4", 4), materials=(6, capi.MATERIAL_DTYPE, None), light_tri_idx=(7, "<i4", None),
+          light_cdf=(8, "<f4", None), env_probs=(9, "<f4", None), env_aliases=(10, "<i4", None), env_pdf=(11, "<f4", None))
+LBVH = dict(aabb_min=(0, "<f4", 4), aabb_max=(1, "<f4", 4), centroid=(2, "<f4", 4), primitive_indices=(3, "<i4", None),
+            morton_codes=(4, "<u8", None), child_nodes=(5, "<i4", 2), parent=(6, "<i4", None),
+            escape_indices=(7, "<i4", None), world_aabb=(8, "<f4", 4))
+PATH_FIELDS = dict(ray_ori=(0, "<f4", 4), ray_dir_dist=(1, "<f4", 4), hit_uv=(2, "<f4", 4), throughput_pdf=(3, "<f4", 4),
+                   hit_geom_id=(4, "<i4", None), material_id=(5, "<i4", None), remaining_bounces=(6, "<i4", None),
+                   rng_state=(7, "<u4", None))
+QUEUES = dict(extension=0, shadow=1, pbr=2, diffuse=3, reflection=4, refraction=5)
+
+
+def _fetch(getter, handle, spec):
+    which, dtype, width = spec
+    size = check(getter(handle, which, None, 0))
+    dt = np.dtype(dtype)
+    out = np.empty(size // dt.itemsize, dtype=dt)
+    if size:
+        check(getter(handle, which, ptr(out), size))
+    return out.reshape(-1, width) if width else out
+
+
+class Scene:
+    """`class Scene` of the reference (src/scene.h:51-92): same scene.json schema and semantics."""
+
+    def __init__(self, filename=None, _handle=None):
+        self._h = C.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+        else:
+            check(lib.ptb_scene_load(str(filename).encode(), C.byref(self._h)))
+
+    @classmethod
+    def from_arrays(cls, pos, nor, indices, material_ids, materials, camera, uv=None, tangent=None, trace_depth=8):
+        """camera: dict(resolution=(w,h), fovy=deg, eye=, look_at=, up=)."""
+        pos = np.ascontiguousarray(pos, dtype=np.float32).reshape(-1, 3)
+        nor = np.ascontiguousarray(nor, dtype=np.float32).reshape(-1, 3)
+        indices = np.ascontiguousarray(indices, dtype=np.int32).reshape(-1, 3)
+        material_ids = np.ascontiguousarray(material_ids, dtype=np.int32).reshape(-1)
+        materials = np.ascontiguousarray(materials, dtype=capi.MATERIAL_DTYPE)
+        uv = None if uv is None else np.ascontiguousarray(uv, dtype=np.float32).reshape(-1, 2)
+        tangent = None if tangent is None else np.ascontiguousarray(tangent, dtype=np.float32).reshape(-1, 3)
+        cam = capi.Camera()
+        cam.resolution[0], cam.resolution[1] = camera["resolution"]
+        h = C.c_void_p()
+        check(lib.ptb_scene_from_arrays(ptr(pos), ptr(nor), ptr(uv), ptr(tangent), pos.shape[0], ptr(indices),
+                                        ptr(material_ids), indices.shape[0], ptr(materials), materials.shape[0],
+                                        C.byref(cam), trace_depth, C.byref(h)))
+        s = cls(_handle=h)
+        s.set_camera(camera["resolution"], camera["fovy"], camera["eye"], camera["look_at"], camera["up"], trace_depth)
+        return s
+
+    def set_camera(self, resolution, fovy, eye, look_at, up, trace_depth=0):
+        res = (C.c_int32 * 2)(*resolution)
+        e, l, u = (C.c_float * 3)(*eye), (C.c_float * 3)(*look_at), (C.c_float * 3)(*up)
+        check(lib.ptb_scene_set_camera(self._h, C.byref(res), float(fovy), C.byref(e), C.byref(l), C.byref(u), trace_depth))
+
+    def set_environment(self, rgb):
+        rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+        h, w, _ = rgb.shape
+        check(lib.ptb_scene_set_environment(self._h, ptr(rgb), w, h))
+
+    @property
+    def info(self):
+        i = capi.SceneInfo()
+        check(lib.ptb_scene_get_info(self._h, C.byref(i)))
+        return i
+
+    @property
+    def camera(self):
+        c = capi.Camera()
+        check(lib.ptb_scene_get_camera(self._h, C.byref(c)))
+        return c
+
+    def array(self, name):
+        return _fetch(lib.ptb_scene_get_array, self._h, SA[name])
+
+    def free(self):
+        if self._h:
+            lib.ptb_scene_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Renderer:
+    """An opaque ptb_renderer: PathtraceInit / Pathtrace / PathtraceFree on a handle."""
+
+    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True):
+        cfg = capi.Config()
+        lib.ptb_config_default(C.byref(cfg))
+        cfg.device, cfg.trace_depth, cfg.rank, cfg.world, cfg.stripe_rows = device, trace_depth, rank, world, stripe_rows
+        cfg.use_graph = 1 if use_graph else 0
+        self._h = C.c_void_p()
+        check(lib.ptb_init(scene._h, C.byref(cfg), C.byref(self._h)))
+        t = capi.TileInfo()
+        check(lib.ptb_get_tile_info(self._h, C.byref(t)))
+        self.width, self.height, self.owned_pixels = t.width, t.height, t.owned_pixels
+        self.rank, self.world, self.stripe_rows = t.rank, t.world, t.stripe_rows
+
+    # -- Pathtrace(pbo, frame, iter) --------------------------------------------------------------
+    def render(self, iteration, count=1):
+        check(lib.ptb_render_many(self._h, iteration, count))
+
+    def sync(self):
+        check(lib.ptb_sync(self._h))
+
+    def resolve(self, iteration, fmt=capi.IMG_MEAN_RGB32F, out=None):
+        """(direct + indirect) / iteration for the owned pixels, into a host array."""
+        if fmt == capi.IMG_RGBA8:
+            out = np.empty((self.owned_pixels, 4), dtype=np.uint8) if out is None else out
+        else:
+            out = np.empty((self.owned_pixels, 3), dtype=np.float32) if out is None else out
+        check(lib.ptb_resolve(self._h, ptr(out), fmt, iteration, 0))
+        return out
+
+    def resolve_device(self, device_ptr, iteration, fmt=capi.IMG_MEAN_RGB32F):
+        check(lib.ptb_resolve(self._h, C.c_void_p(device_ptr), fmt, iteration, 1))
+
+    def set_stream(self, cuda_stream):
+        check(lib.ptb_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def accumulators(self):
+        d = np.empty((self.owned_pixels, 3), dtype=np.float32)
+        i = np.empty((self.owned_pixels, 3), dtype=np.float32)
+        check(lib.ptb_get_accumulators(self._h, ptr(d), ptr(i)))
+        return d, i
+
+    def owned_pixel_indices(self):
+        out = np.empty(self.owned_pixels, dtype=np.int32)
+        check(lib.ptb_get_owned_pixels(self._h, ptr(out), out.size))
+        return out
+
+    # -- parity views -----------------------------------------------------------------------------
+    def lbvh(self, name):
+        return _fetch(lib.ptb_get_lbvh, self._h, LBVH[name])
+
+    def stage(self, stage, iteration=0):
+        check(lib.ptb_stage_run(self._h, stage, iteration))
+
+    def queue_count(self, name):
+        n = C.c_int32()
+        check(lib.ptb_get_queue_count(self._h, QUEUES[name], C.byref(n)))
+        return n.value
+
+    def queue(self, name):
+        n = self.queue_count(name)
+        out = np.empty(max(n, 1), dtype=np.int32)
+        check(lib.ptb_get_queue(self._h, QUEUES[name], ptr(out), n))
+        return out[:n]
+
+    def shadow_queue(self):
+        n = self.queue_count("shadow")
+        m = max(n, 1)
+        o, d, r = (np.empty((m, 4), dtype=np.float32) for _ in range(3))
+        p = np.empty(m, dtype=np.int32)
+        check(lib.ptb_get_shadow_queue(self._h, ptr(o), ptr(d), ptr(r), ptr(p), n))
+        return o[:n], d[:n], r[:n], p[:n]
+
+    def path_field(self, name):
+        which, dtype, width = PATH_FIELDS[name]
+        n = self.width * self.height
+        out = np.zeros((n, width) if width else n, dtype=dtype)
+        check(lib.ptb_get_path_field(self._h, which, ptr(out), out.nbytes))
+        return out
+
+    # -- batched RayCast --------------------------------------------------------------------------
+    def trace_closest(self, ori4, dir4):
+        ori4 = np.ascontiguousarray(ori4, dtype=np.float32).reshape(-1, 4)
+        dir4 = np.ascontiguousarray(dir4, dtype=np.float32).reshape(-1, 4)
+        n = ori4.shape[0]
+        hit = np.empty(n, dtype=np.int32)
+        t, u, v = (np.empty(n, dtype=np.float32) for _ in range(3))
+        check(lib.ptb_trace_closest(self._h, ptr(ori4), ptr(dir4), n, ptr(hit), ptr(t), ptr(u), ptr(v)))
+        return hit, t, u, v
+
+    def trace_occluded(self, ori_tmax4, dir4):
+        ori_tmax4 = np.ascontiguousarray(ori_tmax4, dtype=np.float32).reshape(-1, 4)
+        dir4 = np.ascontiguousarray(dir4, dtype=np.float32).reshape(-1, 4)
+        n = ori_tmax4.shape[0]
+        occ = np.empty(n, dtype=np.int32)
+        check(lib.ptb_trace_occluded(self._h, ptr(ori_tmax4), ptr(dir4), n, ptr(occ)))
+        return occ
+
+    def time_raycast(self, count):
+        ms, rays = C.c_float(), C.c_int32()
+        check(lib.ptb_time_raycast(self._h, count, C.byref(ms), C.byref(rays)))
+        return ms.value, rays.value
+
+    def stats(self):
+        s = capi.Stats()
+        check(lib.ptb_get_stats(self._h, C.byref(s)))
+        return s
+
+    def stats_reset(self):
+        check(lib.ptb_stats_reset(self._h))
+
+    def free(self):
+        if self._h:
+            check(lib.ptb_free(self._h))
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def build_lbvh(pos4, indices_matid4, device=0):
+    """BuildLBVH (src/bvh.h:7) on host arrays; returns the reference-layout arrays and the build time."""
+    pos4 = np.ascontiguousarray(pos4, dtype=np.float32).reshape(-1, 4)
+    im = np.ascontiguousarray(indices_matid4, dtype=np.int32).reshape(-1, 4)
+    V, N = pos4.shape[0], im.shape[0]
+    out = dict(morton_codes=np.empty(max(N, 1), np.uint64), primitive_indices=np.empty(2 * max(N, 1), np.int32),
+               child_nodes=np.empty((max(N - 1, 1), 2), np.int32), parent=np.empty(2 * max(N, 1), np.int32),
+               escape_indices=np.empty(2 * max(N, 1), np.int32), aabb_min=np.empty((2 * max(N, 1), 4), np.float32),
+               aabb_max=np.empty((2 * max(N, 1), 4), np.float32), world_aabb=np.empty((2, 4), np.float32))
+    ms = C.c_float()
+    check(lib.ptb_build_lbvh(device, ptr(pos4), V, ptr(im), N, ptr(out["morton_codes"]), ptr(out["primitive_indices"]),
+                             ptr(out["child_nodes"]), ptr(out["parent"]), ptr(out["escape_indices"]), ptr(out["aabb_min"]),
+                             ptr(out["aabb_max"]), ptr(out["world_aabb"]), C.cast(C.byref(ms), C.c_void_p)))
+    out["build_ms"] = ms.value
+    return out
+
+
+# ---- the reference's process-global front-end (src/pathtrace_wavefront.cu:118-181,205) ----------
+_state = {"renderer": None, "scene": None}
+
+
+def PathtraceInit(scene, **kw):
+    if _state["renderer"] is None:
+        _state["renderer"] = Renderer(scene, **kw)
+        _state["scene"] = scene
+    return _state["renderer"]
+
+
+def Pathtrace(pbo=None, frame=0, iteration=1):
+    """One sample per pixel; `pbo`, if given, is a host uint8 (P,4) array that receives the tonemapped frame."""
+    r = _state["renderer"]
+    if r is None:
+        print("[Wavefront] Error: Render called before Init!")  # src/pathtrace_wavefront.cu:207-210
+        return
+    r.render(iteration)
+    if pbo is not None:
+        r.resolve(iteration, capi.IMG_RGBA8, out=pbo)
+
+
+def PathtraceFree():
+    if _state["renderer"] is not None:
+        _state["renderer"].free()
+    _state["renderer"] = None
+    _state["scene"] = None
