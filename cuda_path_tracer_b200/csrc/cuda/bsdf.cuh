@@ -2,10 +2,22 @@
 // Same models and the same float expression shapes as the reference (src/interactions.cu), so
 // that nvcc's FMA contraction lands on the same operations and per-path decisions (lobe choice,
 // reflect vs. refract, back-face kills) agree with the reference sample by sample.
+//
+// PTB_BSDF_ENTRY: the seven functions the reference's Shading kernels reach ACROSS a translation
+// unit (SampleLight, evalBSDF, pdfBSDF, samplePBR, sampleDiffuse, sampleSpecularReflection,
+// sampleSpecularRefraction; src/interactions.h) are real calls there (-rdc, no LTO), so the
+// optimizer never sees e.g. that `wo` is a negated ray direction -- and the contraction of
+// dot(N, wo) differs from that of dot(N, -dir) (read off the reference's SASS).  They are kept
+// as non-inlined entry points with the reference's by-reference / by-value argument passing, which
+// reproduces those boundaries; everything they call is inlined, as it is in the reference build.
 #pragma once
 #include "common.cuh"
 
+#define PTB_BSDF_ENTRY static __device__ __noinline__
+
 namespace ptb {
+
+struct Vec2 { float x, y; };
 
 struct Mat {          // `Material`, src/scene_structs.h:52-65
     Vec3 basecolor;
@@ -13,7 +25,7 @@ struct Mat {          // `Material`, src/scene_structs.h:52-65
     int type, diffuse_tex, normal_tex, mr_tex;
 };
 
-__device__ __forceinline__ Mat load_material(const ptb_material* __restrict__ mats, int id) {
+static __device__ Mat load_material(const ptb_material* __restrict__ mats, int id) {
     const float4* p = reinterpret_cast<const float4*>(mats + id);
     float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
     Mat m;
@@ -25,7 +37,7 @@ __device__ __forceinline__ Mat load_material(const ptb_material* __restrict__ ma
 }
 
 // LocalToWorld, src/interactions.cu:6-15
-__device__ __forceinline__ Vec3 local_to_world(Vec3 l, Vec3 N) {
+static __device__ Vec3 local_to_world(V3R l, V3R N) {
     Vec3 helper;
     if (fabsf(N.x) < 0.57735027f) helper = Vec3(1.0f, 0.0f, 0.0f);
     else if (fabsf(N.y) < 0.57735027f) helper = Vec3(0.0f, 1.0f, 0.0f);
@@ -36,19 +48,19 @@ __device__ __forceinline__ Vec3 local_to_world(Vec3 l, Vec3 N) {
 }
 
 // FresnelSchlick, src/interactions.cu:17-27
-__device__ __forceinline__ Vec3 fresnel_schlick3(Vec3 F0, float cos_theta) {
+static __device__ Vec3 fresnel_schlick3(Vec3 F0, float cos_theta) {
     float x = clampf(1.0f - cos_theta, 0.0f, 1.0f);
     float x5 = x * x * x * x * x;
     return F0 + (Vec3(1.0f) - F0) * x5;
 }
-__device__ __forceinline__ float fresnel_schlick1(float F0, float cos_theta) {
+static __device__ float fresnel_schlick1(float F0, float cos_theta) {
     float x = clampf(1.0f - cos_theta, 0.0f, 1.0f);
     float x5 = x * x * x * x * x;
     return F0 + (1.0f - F0) * x5;
 }
 
 // DistributionGGX, src/interactions.cu:29-37
-__device__ __forceinline__ float ggx_d(Vec3 N, Vec3 H, float roughness) {
+static __device__ float ggx_d(Vec3 N, Vec3 H, float roughness) {
     float a = roughness * roughness;
     float a2 = a * a;
     float NdotH = fmaxf(dot3(N, H), 0.0f);
@@ -59,12 +71,12 @@ __device__ __forceinline__ float ggx_d(Vec3 N, Vec3 H, float roughness) {
 }
 
 // GeometrySchlickGGX / GeometrySmith, src/interactions.cu:39-51
-__device__ __forceinline__ float smith_g1(float NdotV, float roughness) {
+static __device__ float smith_g1(float NdotV, float roughness) {
     float r = roughness + 1.0f;
     float k = (r * r) / 8.0f;
     return NdotV / (NdotV * (1.0f - k) + k);
 }
-__device__ __forceinline__ float smith_g(Vec3 N, Vec3 V, Vec3 L, float roughness) {
+static __device__ float smith_g(Vec3 N, Vec3 V, Vec3 L, float roughness) {
     float NdotV = fmaxf(dot3(N, V), 0.0f);
     float NdotL = fmaxf(dot3(N, L), 0.0f);
     float ggx2 = smith_g1(NdotV, roughness);
@@ -73,19 +85,19 @@ __device__ __forceinline__ float smith_g(Vec3 N, Vec3 V, Vec3 L, float roughness
 }
 
 // CosineWeightedSampling, src/interactions.cu:53-61
-__device__ __forceinline__ Vec3 sample_cosine(Vec3 N, float xi_x, float xi_y) {
-    float up = sqrtf(xi_x);
+static __device__ Vec3 sample_cosine(V3R N, const Vec2& xi) {
+    float up = sqrtf(xi.x);
     float over = sqrtf(1.0f - up * up);
-    float around = xi_y * PTB_TWO_PI;
+    float around = xi.y * PTB_TWO_PI;
     Vec3 l(cosf(around) * over, sinf(around) * over, up);
     return local_to_world(l, N);
 }
 
 // NDFImportanceSampling, src/interactions.cu:63-76
-__device__ __forceinline__ Vec3 sample_ggx_reflect(Vec3 N, Vec3 wo, float roughness, float xi_x, float xi_y) {
+static __device__ Vec3 sample_ggx_reflect(V3R N, V3R wo, float roughness, const Vec2& xi) {
     float a = roughness * roughness;
-    float phi = PTB_TWO_PI * xi_x;
-    float cos_theta = sqrtf((1.0f - xi_y) / (1.0f + (a * a - 1.0f) * xi_y));
+    float phi = PTB_TWO_PI * xi.x;
+    float cos_theta = sqrtf((1.0f - xi.y) / (1.0f + (a * a - 1.0f) * xi.y));
     float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
     Vec3 h_local(sin_theta * cosf(phi), sin_theta * sinf(phi), cos_theta);
     Vec3 H = local_to_world(h_local, N);
@@ -93,7 +105,7 @@ __device__ __forceinline__ Vec3 sample_ggx_reflect(Vec3 N, Vec3 wo, float roughn
 }
 
 // CalculateSpecularProbability, src/interactions.cu:80-90
-__device__ __forceinline__ float specular_probability(const Mat& m, Vec3 N, Vec3 V) {
+static __device__ float specular_probability(const Mat& m, V3R N, V3R V) {
     Vec3 F0 = mix3(Vec3(0.04f), m.basecolor, m.metallic);
     Vec3 F = fresnel_schlick3(F0, fmaxf(dot3(N, V), 0.0f));
     float p = (F.x + F.y + F.z) / 3.0f;
@@ -102,7 +114,7 @@ __device__ __forceinline__ float specular_probability(const Mat& m, Vec3 N, Vec3
 }
 
 // evalPBR, src/interactions.cu:96-124
-__device__ __forceinline__ Vec3 eval_pbr(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+static __device__ Vec3 eval_pbr(V3R wo, V3R wi, V3R N, const Mat& m) {
     float NdotL = dot3(N, wi);
     float NdotV = dot3(N, wo);
     if (NdotL <= 0.0f) return Vec3(0.0f);
@@ -123,7 +135,7 @@ __device__ __forceinline__ Vec3 eval_pbr(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m)
 }
 
 // pdfPBR, src/interactions.cu:148-171
-__device__ __forceinline__ float pdf_pbr(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+static __device__ float pdf_pbr(V3R wo, V3R wi, V3R N, const Mat& m) {
     float NdotL = dot3(N, wi);
     if (NdotL <= 0.0f) return 0.0f;
     Vec3 H = normalize3(wo + wi);
@@ -138,33 +150,38 @@ __device__ __forceinline__ float pdf_pbr(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m)
     return spec_prob * pdf_spec + diff_prob * pdf_diff;
 }
 
+// evalDiffuse, src/interactions.cu:127-129
+static __device__ Vec3 eval_diffuse(const Mat& m, V3R N, V3R wi) { return m.basecolor * PTB_INV_PI; }
+
 // evalBSDF / pdfBSDF for the two materials that do NEE (src/interactions.cu:191-216)
-__device__ __forceinline__ Vec3 eval_bsdf(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+PTB_BSDF_ENTRY Vec3 eval_bsdf(Vec3 wo, Vec3 wi, Vec3 N, Mat m) {
     if (m.type == MAT_PBR) return eval_pbr(wo, wi, N, m);
-    if (m.type == MAT_DIFFUSE) return m.basecolor * PTB_INV_PI;
-    return Vec3(0.0f);
+    else if (m.type == MAT_DIFFUSE) return eval_diffuse(m, N, wi);
+    else return Vec3(0.0f);
 }
-__device__ __forceinline__ float pdf_diffuse(Vec3 wi, Vec3 N) {
+static __device__ float pdf_diffuse(V3R wi, V3R N) {
     float NdotL = dot3(N, wi);
     if (NdotL <= 0.0f) return 0.0f;
     return NdotL * PTB_INV_PI;
 }
-__device__ __forceinline__ float pdf_bsdf(Vec3 wo, Vec3 wi, Vec3 N, const Mat& m) {
+PTB_BSDF_ENTRY float pdf_bsdf(Vec3 wo, Vec3 wi, Vec3 N, Mat m) {
     if (m.type == MAT_PBR) return pdf_pbr(wo, wi, N, m);
-    if (m.type == MAT_DIFFUSE) return pdf_diffuse(wi, N);
-    return PTB_PDF_DIRAC_DELTA;
+    else if (m.type == MAT_DIFFUSE) return pdf_diffuse(wi, N);
+    else if (m.type == MAT_REFLECT) return PTB_PDF_DIRAC_DELTA;
+    else return PTB_PDF_DIRAC_DELTA;
 }
 
 // samplePBR, src/interactions.cu:223-253.  Draw order is the DEVICE order of the reference
 // build: xi.x = 1st draw, xi.y = 2nd, lobe selector = 3rd.
-__device__ __forceinline__ Vec3 sample_pbr(Vec3 wo, Vec3& wi, float& pdf, Vec3 N, const Mat& m, uint32_t& seed) {
-    float xi_x = rand_float(seed);
-    float xi_y = rand_float(seed);
+PTB_BSDF_ENTRY Vec3 sample_pbr(const Vec3& wo, Vec3& wi, float& pdf, const Vec3& N, const Mat& m, uint32_t& seed) {
+    Vec2 xi;
+    xi.x = rand_float(seed);   // device evaluation order of glm::vec2(rand, rand): x first
+    xi.y = rand_float(seed);
     float r_select = rand_float(seed);
     float roughness = clampf(m.roughness, 0.01f, 1.0f);
     float spec_prob = specular_probability(m, N, wo);
-    if (r_select < spec_prob) wi = sample_ggx_reflect(N, wo, roughness, xi_x, xi_y);
-    else wi = sample_cosine(N, xi_x, xi_y);
+    if (r_select < spec_prob) wi = sample_ggx_reflect(N, wo, roughness, xi);
+    else wi = sample_cosine(N, xi);
     wi = normalize3(wi);
     if (dot3(N, wi) <= 0.0f) { pdf = 0.0f; return Vec3(0.0f); }
     pdf = pdf_pbr(wo, wi, N, m);
@@ -173,18 +190,19 @@ __device__ __forceinline__ Vec3 sample_pbr(Vec3 wo, Vec3& wi, float& pdf, Vec3 N
 }
 
 // sampleDiffuse, src/interactions.cu:323-338
-__device__ __forceinline__ Vec3 sample_diffuse(Vec3& wi, float& pdf, Vec3 N, const Mat& m, uint32_t& seed) {
-    float xi_x = rand_float(seed);
-    float xi_y = rand_float(seed);
-    wi = sample_cosine(N, xi_x, xi_y);
+PTB_BSDF_ENTRY Vec3 sample_diffuse(const Vec3& wo, Vec3& wi, float& pdf, const Vec3& N, const Mat& m, uint32_t& seed) {
+    Vec2 xi;
+    xi.x = rand_float(seed);
+    xi.y = rand_float(seed);
+    wi = sample_cosine(N, xi);
     if (dot3(N, wi) <= 0.0f) { pdf = 0.0f; return Vec3(0.0f); }
     pdf = pdf_diffuse(wi, N);
-    Vec3 fr = m.basecolor * PTB_INV_PI;
+    Vec3 fr = eval_diffuse(m, N, wi);
     return fr * fmaxf(0.0f, dot3(N, wi)) / fmaxf(pdf, PTB_EPSILON);
 }
 
 // sampleSpecularReflection, src/interactions.cu:340-354
-__device__ __forceinline__ Vec3 sample_mirror(Vec3 wo, Vec3& wi, float& pdf, Vec3 N, const Mat& m) {
+PTB_BSDF_ENTRY Vec3 sample_mirror(const Vec3& wo, Vec3& wi, float& pdf, const Vec3& N, const Mat& m) {
     wi = reflect3(-wo, N);
     float NdotWi = fmaxf(dot3(N, wi), 0.0f);
     pdf = PTB_PDF_DIRAC_DELTA;
@@ -194,7 +212,7 @@ __device__ __forceinline__ Vec3 sample_mirror(Vec3 wo, Vec3& wi, float& pdf, Vec
 
 // sampleSpecularRefraction, src/interactions.cu:356-397; glm::refract per
 // external/include/glm/detail/func_geometric.inl:194-200.
-__device__ __forceinline__ Vec3 sample_dielectric(Vec3 wo, Vec3& wi, float& pdf, Vec3 N, const Mat& m, uint32_t& seed) {
+PTB_BSDF_ENTRY Vec3 sample_dielectric(const Vec3& wo, Vec3& wi, float& pdf, const Vec3& N, const Mat& m, uint32_t& seed) {
     float n1 = 1.0f, n2 = m.ior;
     Vec3 n_eff = N;
     if (dot3(wo, N) < 0.0f) { n1 = m.ior; n2 = 1.0f; n_eff = -N; }
@@ -220,7 +238,7 @@ __device__ __forceinline__ Vec3 sample_dielectric(Vec3 wo, Vec3& wi, float& pdf,
 }
 
 // BinarySearch, src/common/cuda_utilities.h:199-214
-__device__ __forceinline__ int cdf_search(const float* __restrict__ cdf, int count, float value) {
+static __device__ int cdf_search(const float* __restrict__ cdf, int count, float value) {
     int left = 0, right = count - 1;
     while (left <= right) {
         int mid = left + (right - left) / 2;
@@ -231,8 +249,8 @@ __device__ __forceinline__ int cdf_search(const float* __restrict__ cdf, int cou
 }
 
 // SampleLight, src/interactions.cu:400-445
-__device__ __forceinline__ void sample_light(const MeshDev& mesh, const LightDev& lights, uint32_t& seed,
-                                             Vec3& point, Vec3& normal, float& pdf_area, int& tri_index) {
+PTB_BSDF_ENTRY void sample_light(const MeshDev& mesh, const LightDev& lights, uint32_t& seed,
+                                 Vec3& point, Vec3& normal, float& pdf_area, int& tri_index) {
     float r1 = rand_float(seed);
     float r2 = rand_float(seed);
     float r3 = rand_float(seed);
@@ -249,7 +267,7 @@ __device__ __forceinline__ void sample_light(const MeshDev& mesh, const LightDev
 }
 
 // PowerHeuristic, src/common/cuda_utilities.h:193-197
-__device__ __forceinline__ float power_heuristic(float f, float g) {
+static __device__ float power_heuristic(float f, float g) {
     float f2 = f * f;
     float g2 = g * g;
     return f2 / (f2 + g2 + 1e-5f);

@@ -27,34 +27,56 @@ namespace ptb {
 
 enum { MAT_PBR = 0, MAT_DIFFUSE = 1, MAT_REFLECT = 2, MAT_REFRACT = 3 };
 
+// Like glm::tvec3 (detail/type_vec3.hpp) this type has user-provided default/copy constructors and
+// assignment.  That is deliberate: it makes the type non-trivially-copyable, so a `Vec3` passed "by
+// value" to a non-inlined function travels by hidden reference, as glm::vec3 does in the reference's
+// evalBSDF / pdfBSDF -- and the loads-vs-registers difference changes nvcc's FMA choices.
 struct Vec3 {
     float x, y, z;
-    __host__ __device__ Vec3() {}
+    __host__ __device__ Vec3() : x(0.0f), y(0.0f), z(0.0f) {}
+    __host__ __device__ Vec3(const Vec3& v) : x(v.x), y(v.y), z(v.z) {}
     __host__ __device__ Vec3(float a, float b, float c) : x(a), y(b), z(c) {}
     __host__ __device__ explicit Vec3(float a) : x(a), y(a), z(a) {}
+    __host__ __device__ Vec3& operator=(const Vec3& v) { x = v.x; y = v.y; z = v.z; return *this; }
 };
-__device__ __forceinline__ Vec3 operator+(Vec3 a, Vec3 b) { return Vec3(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ Vec3 operator-(Vec3 a, Vec3 b) { return Vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ Vec3 operator-(Vec3 a) { return Vec3(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ Vec3 operator*(Vec3 a, Vec3 b) { return Vec3(a.x * b.x, a.y * b.y, a.z * b.z); }
-__device__ __forceinline__ Vec3 operator*(Vec3 a, float s) { return Vec3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ Vec3 operator*(float s, Vec3 a) { return Vec3(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ Vec3 operator/(Vec3 a, float s) { return Vec3(a.x / s, a.y / s, a.z / s); }
-__device__ __forceinline__ Vec3 operator+(Vec3 a, float s) { return Vec3(a.x + s, a.y + s, a.z + s); }
+// Operators take their operands by const reference, exactly like GLM's tvec3 operators
+// (detail/type_vec3.inl): argument passing changes the order in which nvcc sees the operations and
+// with it which product of `a*b + c*d` gets fused (checked on PTX, tools/ptx_alpha.py).
+typedef const Vec3& V3R;
+__device__ __forceinline__ Vec3 operator+(V3R a, V3R b) { return Vec3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ Vec3 operator-(V3R a, V3R b) { return Vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ Vec3 operator-(V3R a) { return Vec3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ Vec3 operator*(V3R a, V3R b) { return Vec3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ Vec3 operator*(V3R a, const float& s) { return Vec3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ Vec3 operator*(const float& s, V3R a) { return Vec3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ Vec3 operator/(V3R a, const float& s) { return Vec3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ Vec3 operator+(V3R a, const float& s) { return Vec3(a.x + s, a.y + s, a.z + s); }
 __device__ __forceinline__ Vec3 make_v3(float4 f) { return Vec3(f.x, f.y, f.z); }
 
-__device__ __forceinline__ float dot3(Vec3 a, Vec3 b) {
+// Two flavours of the GLM geometric functions:
+//  * dot3 / cross3 / length3 / normalize3 are written exactly like GLM 0.9.6.3 writes them
+//    (detail/func_geometric.inl:65-72,134-142,154-159) and left to nvcc's FMA contraction.  Which
+//    product ends up rounded depends on the surrounding expression (e.g. dot(N, -wo) contracts
+//    differently from dot(N, wo) -- read off the reference's SASS), so the shading code, which must
+//    land on the reference's contraction, uses these and mirrors the reference's expression shapes.
+//  * *_pinned spell out the contraction of the reference's intersection routines (SURVEY.md
+//    Appendix B.3) with explicit intrinsics; the RayCast stage uses them.
+__device__ __forceinline__ float dot3(V3R a, V3R b) {
+    Vec3 tmp(a.x * b.x, a.y * b.y, a.z * b.z);
+    return tmp.x + tmp.y + tmp.z;
+}
+__device__ __forceinline__ Vec3 cross3(V3R x, V3R y) {
+    return Vec3(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y);
+}
+__device__ __forceinline__ float length3(V3R v) { return sqrtf(dot3(v, v)); }
+__device__ __forceinline__ Vec3 normalize3(V3R v) { return v * (1.0f / sqrtf(dot3(v, v))); }
+__device__ __forceinline__ float dot3_pinned(Vec3 a, Vec3 b) {
     return __fmaf_rn(a.z, b.z, __fmaf_rn(a.x, b.x, __fmul_rn(a.y, b.y)));
 }
-__device__ __forceinline__ Vec3 cross3(Vec3 a, Vec3 b) {
+__device__ __forceinline__ Vec3 cross3_pinned(Vec3 a, Vec3 b) {
     return Vec3(__fmaf_rn(a.y, b.z, -__fmul_rn(b.y, a.z)),
-              __fmaf_rn(a.z, b.x, -__fmul_rn(b.z, a.x)),
-              __fmaf_rn(a.x, b.y, -__fmul_rn(b.x, a.y)));
-}
-__device__ __forceinline__ float length3(Vec3 v) { return __fsqrt_rn(dot3(v, v)); }
-__device__ __forceinline__ Vec3 normalize3(Vec3 v) {
-    float inv = __frcp_rn(__fsqrt_rn(dot3(v, v)));
-    return Vec3(__fmul_rn(v.x, inv), __fmul_rn(v.y, inv), __fmul_rn(v.z, inv));
+                __fmaf_rn(a.z, b.x, -__fmul_rn(b.z, a.x)),
+                __fmaf_rn(a.x, b.y, -__fmul_rn(b.x, a.y)));
 }
 // glm::min / glm::max / glm::clamp (detail/func_common.inl:409-456): plain comparisons, so a NaN
 // argument propagates the way it does in the reference (fminf/fmaxf would drop it).
@@ -63,10 +85,10 @@ __device__ __forceinline__ float glm_max(float x, float y) { return x > y ? x : 
 __device__ __forceinline__ float clampf(float x, float lo, float hi) { return glm_min(glm_max(x, lo), hi); }
 // glm::mix (detail/func_common.inl:74-105): x + a * (y - x)
 __device__ __forceinline__ float mixf(float x, float y, float a) { return x + a * (y - x); }
-__device__ __forceinline__ Vec3 mix3(Vec3 x, Vec3 y, float a) { return x + a * (y - x); }
-__device__ __forceinline__ Vec3 operator/(Vec3 a, Vec3 b) { return Vec3(a.x / b.x, a.y / b.y, a.z / b.z); }
+__device__ __forceinline__ Vec3 mix3(V3R x, V3R y, const float& a) { return x + a * (y - x); }
+__device__ __forceinline__ Vec3 operator/(V3R a, V3R b) { return Vec3(a.x / b.x, a.y / b.y, a.z / b.z); }
 // glm::reflect (detail/func_geometric.inl:176-180): I - N * dot(N, I) * 2
-__device__ __forceinline__ Vec3 reflect3(Vec3 I, Vec3 N) { return I - N * dot3(N, I) * 2.0f; }
+__device__ __forceinline__ Vec3 reflect3(V3R I, V3R N) { return I - N * dot3(N, I) * 2.0f; }
 
 // ---- RNG (src/rng.h:6-27) ---------------------------------------------------------------------
 __host__ __device__ __forceinline__ uint32_t wang_hash(uint32_t seed) {
@@ -81,7 +103,7 @@ __device__ __forceinline__ float rand_float(uint32_t& state) {
     state ^= state << 13;
     state ^= state >> 17;
     state ^= state << 5;
-    return __fmul_rn(__uint2float_rn(state), 2.3283064365386963e-10f);
+    return state * 2.3283064365386963e-10f;
 }
 
 // ---- scene on the device ------------------------------------------------------------------------

@@ -42,17 +42,17 @@ __device__ __forceinline__ float slab_test(float4 mn, float4 mx, Vec3 o, Vec3 in
 __device__ __forceinline__ float triangle_test(Vec3 v0, Vec3 v1, Vec3 v2, Vec3 o, Vec3 d, float& out_u, float& out_v) {
     Vec3 e1(__fsub_rn(v1.x, v0.x), __fsub_rn(v1.y, v0.y), __fsub_rn(v1.z, v0.z));
     Vec3 e2(__fsub_rn(v2.x, v0.x), __fsub_rn(v2.y, v0.y), __fsub_rn(v2.z, v0.z));
-    Vec3 pvec = cross3(d, e2);
-    float det = dot3(e1, pvec);
+    Vec3 pvec = cross3_pinned(d, e2);
+    float det = dot3_pinned(e1, pvec);
     if (fabsf(det) < PTB_EPSILON) return -1.0f;
     float inv_det = __frcp_rn(det);
     Vec3 tvec(__fsub_rn(o.x, v0.x), __fsub_rn(o.y, v0.y), __fsub_rn(o.z, v0.z));
-    out_u = __fmul_rn(dot3(tvec, pvec), inv_det);
+    out_u = __fmul_rn(dot3_pinned(tvec, pvec), inv_det);
     if (out_u < 0.0f || out_u > 1.0f) return -1.0f;
-    Vec3 qvec = cross3(tvec, e1);
-    out_v = __fmul_rn(dot3(d, qvec), inv_det);
+    Vec3 qvec = cross3_pinned(tvec, e1);
+    out_v = __fmul_rn(dot3_pinned(d, qvec), inv_det);
     if (out_v < 0.0f || __fadd_rn(out_u, out_v) > 1.0f) return -1.0f;
-    float t = __fmul_rn(dot3(e2, qvec), inv_det);
+    float t = __fmul_rn(dot3_pinned(e2, qvec), inv_det);
     return (t > 1e-7f) ? t : -1.0f;
 }
 

@@ -248,7 +248,7 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
     float next_pdf = 0.0f;
     Vec3 att;
     if (TYPE == MAT_PBR) att = sample_pbr(wo, next_dir, next_pdf, N, m, seed);
-    else if (TYPE == MAT_DIFFUSE) att = sample_diffuse(next_dir, next_pdf, N, m, seed);
+    else if (TYPE == MAT_DIFFUSE) att = sample_diffuse(wo, next_dir, next_pdf, N, m, seed);
     else if (TYPE == MAT_REFLECT) att = sample_mirror(wo, next_dir, next_pdf, N, m);
     else att = sample_dielectric(wo, next_dir, next_pdf, N, m, seed);
 

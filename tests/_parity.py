@@ -128,7 +128,8 @@ def compare_staged_frame(ref, renderer, iteration, depth):
     P = renderer.width * renderer.height
     counters = ref.load("counters", "<i4", 6)
     renderer.stage(capi.STAGE_RAYGEN, iteration)
-    d = _state_diff(ref, "raygen", renderer)
+    # RayGen does not write hit_normal (stale memory on both sides, src/kernels/ray_gen.cu:65-75)
+    d = _state_diff(ref, "raygen", renderer, None, ("ray_ori", "ray_dir_dist", "throughput_pdf", "hit_geom_id", "material_id", "remaining_bounces", "rng_state"))
     rep["raygen"] = d
     if any(d.values()):
         rep["ok"] = False

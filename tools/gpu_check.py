@@ -85,6 +85,39 @@ def timing_case(name, scene_json, frames=20, warm=3):
     print("timing", name, rep, flush=True)
 
 
+def debug_shade(scene_json, name, step_limit=1):
+    """Break step-0 shading mismatches down by material queue and print examples."""
+    from cuda_path_tracer_b200 import capi
+    d = f"/tmp/ref_{name}"
+    if not os.path.exists(os.path.join(d, "meta.json")):
+        par.run_refdump(scene_json, d, iters=1, stages=True)
+    ref = par.RefDump(d)
+    scene = ptb.Scene(scene_json)
+    r = ptb.Renderer(scene)
+    r.stage(capi.STAGE_RAYGEN, 1)
+    for step in range(step_limit):
+        r.stage(capi.STAGE_TRACE); r.stage(capi.STAGE_LOGIC); r.stage(capi.STAGE_SHADE)
+    T = f"s{step_limit - 1}"
+    mats = scene.array("materials")
+    matid = ref.load(T + "_shaded_material_id", "<i4")
+    for qn in ("pbr", "diffuse", "reflection", "refraction"):
+        q = ref.load(f"{T}_{qn}_queue", "<i4")
+        alive = ref.load(T + "_shaded_remaining_bounces", "<i4")[q] >= 0
+        qa = q[alive]
+        line = {"queue": qn, "n": int(q.size), "alive": int(qa.size)}
+        for fld, rname in (("ray_dir_dist", "ray_dir_dist"), ("throughput_pdf", "throughput_pdf"), ("ray_ori", "ray_ori")):
+            a = ref.load(f"{T}_shaded_{rname}", "<f4", 4)[qa]
+            b = r.path_field(fld)[qa]
+            neq = (a.view(np.uint32) != b.view(np.uint32))
+            line[fld] = [int(x) for x in neq.sum(axis=0)]
+            rows = np.nonzero(neq.any(axis=1))[0][:3]
+            for k in rows:
+                ulp = (a[k].view(np.int32).astype(np.int64) - b[k].view(np.int32).astype(np.int64)).tolist()
+                print("   ", qn, fld, "path", int(qa[k]), "mat", int(matid[qa[k]]), "ref", a[k].tolist(), "new", b[k].tolist(), "ulp", ulp)
+        print(line, flush=True)
+    r.free()
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["cornell", "fire_small", "fire", "timing"]
     try:
@@ -94,6 +127,8 @@ if __name__ == "__main__":
             staged_case("fire_small", scenegen.fireplace("/tmp/sc_fire_small", res=(480, 270), scale=0.25)[0])
         if "fire" in which:
             staged_case("fire", scenegen.fireplace("/tmp/sc_fire", res=(1920, 1080))[0])
+        if "debug" in which:
+            debug_shade(scenegen.fireplace("/tmp/sc_fire_small", res=(480, 270), scale=0.25)[0], "fire_small")
         if "timing" in which:
             timing_case("cornell800", scenegen.cornell("/tmp/sc_cornell800", res=(800, 800)))
             timing_case("fire", scenegen.fireplace("/tmp/sc_fire", res=(1920, 1080))[0])
@@ -105,3 +140,4 @@ if __name__ == "__main__":
                 return float(o)
             return str(o)
         json.dump(report, open(os.path.join(OUT, "gpu_check.json"), "w"), indent=1, default=default)
+
