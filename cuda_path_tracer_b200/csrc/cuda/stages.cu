@@ -11,7 +11,8 @@
 //     a warp always shades a single material type (type-uniform control flow, no divergence
 //     between models);
 //   * queue appends are warp-aggregated at a converged point (one atomic per warp per queue);
-//   * each path owns its pixel, so emission / environment adds are plain read-modify-writes.
+//   * each path owns its pixel, so the emission / environment adds never contend (they stay
+//     atomicAdd = fire-and-forget RED, and stay un-fused with the product that feeds them).
 #include "bsdf.cuh"
 #include "render.cuh"
 
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(kThreads) k_logic(FrameDev f, int bounce) {
                         else mis = (pdf_bsdf * pdf_bsdf) / (pdf_bsdf * pdf_bsdf + pdf_env * pdf_env + PTB_EPSILON);
                     }
                     Vec3 add = throughput * env * mis;
-                    pix[0] += add.x; pix[1] += add.y; pix[2] += add.z;
+                    atomicAdd(pix + 0, add.x); atomicAdd(pix + 1, add.y); atomicAdd(pix + 2, add.z);   // a separate add: `pix += a*b` would fuse
                 }
                 f.pool.remaining_bounces[idx] = -1;
             } else {
@@ -157,7 +158,7 @@ __global__ void __launch_bounds__(kThreads) k_logic(FrameDev f, int bounce) {
                         }
                     }
                     Vec3 add = throughput * m.basecolor * m.emittance * mis;
-                    pix[0] += add.x; pix[1] += add.y; pix[2] += add.z;
+                    atomicAdd(pix + 0, add.x); atomicAdd(pix + 1, add.y); atomicAdd(pix + 2, add.z);   // a separate add: `pix += a*b` would fuse
                     f.pool.remaining_bounces[idx] = -1;
                 } else {
                     queue = m.type;

@@ -208,3 +208,23 @@ def radiance_report(ref_direct, ref_indirect, new_direct, new_indirect, iters):
             "bit_mismatch_direct": count_bit_mismatch(ref_direct, new_direct), "bit_mismatch_indirect": count_bit_mismatch(ref_indirect, new_indirect),
             "max_rel_err": float(rel.max()) if rel.size else 0.0, "outliers_gt_1e-4": int((rel > 1e-4).sum()),
             "outlier_fraction": float((rel > 1e-4).mean()) if rel.size else 0.0, "rmse": rmse}
+
+
+def failures(rep):
+    """The non-matching items of a compare_staged_frame report (for assertion messages)."""
+    out = {"raygen": {k: v for k, v in rep["raygen"].items() if v}}
+    for s in rep["steps"]:
+        bad = {}
+        for k, v in s.items():
+            if isinstance(v, dict):
+                if any(v.values()):
+                    bad[k] = {a: b for a, b in v.items() if b}
+            elif k.endswith("mismatch") and v:
+                bad[k] = v
+            elif k.endswith("equal") and not v:
+                bad[k] = v
+            elif k.endswith("count") and v[0] != v[1]:
+                bad[k] = v
+        if bad:
+            out[s["step"]] = bad
+    return out

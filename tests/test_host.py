@@ -1,0 +1,122 @@
+"""CPU: the C-ABI library loads and exports what include/ptb200.h declares; the host scene loader
+reproduces the reference's uploaded arrays (golden); error behaviour without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import cuda_path_tracer_b200 as ptb
+from cuda_path_tracer_b200 import capi, scenegen
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _bits(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.uint8), np.ascontiguousarray(b).view(np.uint8))
+
+
+def test_header_symbols_exported():
+    hdr = open(os.path.join(ROOT, "include", "ptb200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(ptb_[a-z_0-9]+)\s*\(", hdr))
+    assert len(names) >= 30
+    lib = C.CDLL(capi.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in ptb200.h but not exported"
+    assert names == set(capi.SIGNATURES), names ^ set(capi.SIGNATURES)
+    assert capi.lib.ptb_abi_version() == 1
+
+
+def test_struct_layouts():
+    assert C.sizeof(capi.Material) == 48          # reference Material, src/scene_structs.h:52-65
+    assert C.sizeof(capi.Camera) == 4 * (2 + 3 * 5 + 2 + 2)
+    assert C.sizeof(capi.Config) == 4 * 14
+
+
+@pytest.mark.parametrize("case,gen", [("cornell64", lambda d: scenegen.cornell(d, res=(64, 64))),
+                                      ("fire_tiny", lambda d: scenegen.fireplace(d, res=(96, 54), scale=0.1)[0])])
+def test_loader_matches_reference_upload(golden, tmp_path, case, gen):
+    """Scene::Scene + initSceneGeometry (src/scene.cpp:83-631, src/wavefront_internal.cu:118-167)."""
+    g = golden(case)
+    s = ptb.Scene(gen(str(tmp_path / case)))
+    for name, key in (("pos", "mesh_pos"), ("nor", "mesh_nor"), ("uv", "mesh_uv"), ("indices_matid", "mesh_indices_matid"),
+                      ("nor_geom", "mesh_nor_geom"), ("light_tri_idx", "light_tri_idx"), ("light_cdf", "light_cdf")):
+        assert _bits(s.array(name), g[key]), name
+    mine = s.array("materials").view(np.uint8).reshape(-1, 48)[:, :44]
+    assert np.array_equal(mine, g["materials"].reshape(-1, 48)[:, :44])   # _pad is uninitialised in the reference
+    cam = s.camera
+    ref = g["camera"]   # position, view, up, right, fov, pixelLength
+    mine = np.array(list(cam.position) + list(cam.view) + list(cam.up) + list(cam.right) + list(cam.fov) + list(cam.pixel_length), np.float32)
+    assert _bits(mine, ref[:16])
+    n, v, w, h, depth, nmat, nl = g["meta"]
+    i = s.info
+    assert (i.num_triangles, i.num_vertices, i.width, i.height, i.trace_depth, i.num_materials, i.num_lights) == (n, v, w, h, depth, nmat, nl)
+
+
+def test_material_ids_follow_sorted_json_keys(tmp_path):
+    s = ptb.Scene(scenegen.cornell(str(tmp_path / "c"), res=(8, 8)))
+    m = s.array("materials")
+    # green, light, red, white, then one default PBR material appended per object (src/scene.cpp:303-327,467-475)
+    assert np.allclose(m["basecolor"][0], [0.12, 0.45, 0.15]) and m["emittance"][1] == 12.0
+    assert (m["type"][:4] == 1).all() and (m["type"][4:] == 0).all() and len(m) == 4 + 8
+
+
+def test_fireplace_material_mix(tmp_path):
+    path, n = scenegen.fireplace(str(tmp_path / "f"))
+    assert n == 143173
+    s = ptb.Scene(path)
+    counts = np.bincount(s.array("materials")["type"][s.array("indices_matid")[:, 3]], minlength=4)
+    assert counts.tolist() == [24421, 107572, 10, 11170]   # README.md:34
+    assert not np.isnan(s.array("nor")).any()
+
+
+def test_errors_are_codes_not_exits(tmp_path):
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Scene(str(tmp_path / "missing.json"))
+    assert e.value.code in (capi.ERR_IO, capi.ERR_PARSE)
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Scene(str(tmp_path / "scene.txt"))
+    assert e.value.code == capi.ERR_INVALID
+    bad = tmp_path / "bad.json"
+    bad.write_text("{ not json")
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Scene(str(bad))
+    assert e.value.code == capi.ERR_PARSE
+
+
+def test_from_arrays_validation():
+    pos = np.zeros((3, 3), np.float32)
+    nor = np.tile(np.array([[0, 0, 1]], np.float32), (3, 1))
+    mats = scenegen.stress_materials()
+    cam = scenegen.stress_camera((16, 16))
+    with pytest.raises(capi.PtbError):
+        ptb.Scene.from_arrays(pos, nor, [[0, 1, 5]], [0], mats, cam)       # vertex index out of range
+    with pytest.raises(capi.PtbError):
+        ptb.Scene.from_arrays(pos, nor, [[0, 1, 2]], [9], mats, cam)       # material id out of range
+
+
+def test_no_cpu_fallback(tmp_path):
+    """Without a CUDA device every compute entry point fails loudly (PTB_ERR_CUDA)."""
+    if capi.lib.ptb_device_count() > 0:
+        pytest.skip("a GPU is present")
+    s = ptb.Scene(scenegen.cornell(str(tmp_path / "c"), res=(8, 8)))
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Renderer(s)
+    assert e.value.code == capi.ERR_CUDA
+    with pytest.raises(capi.PtbError) as e:
+        ptb.build_lbvh(s.array("pos"), s.array("indices_matid"))
+    assert e.value.code == capi.ERR_CUDA
+
+
+def test_product_does_not_touch_oracle():
+    """The oracle is test infrastructure: no product source may reference it."""
+    pkg = os.path.join(ROOT, "cuda_path_tracer_b200")
+    for dp, _, files in os.walk(pkg):
+        if "build" in dp:
+            continue
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")) or f == "Makefile":
+                text = open(os.path.join(dp, f), errors="replace").read()
+                assert "libptoracle" not in text and "_oracle" not in text and "refdump" not in text.replace("oracle/_ref/refdump) and this library", ""), os.path.join(dp, f)

@@ -1,0 +1,59 @@
+"""CPU (gloo, world_size 2 and 3): tile partition + per-frame gather of the multi-GPU path."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from cuda_path_tracer_b200 import multigpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, width, height, stripe, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    pix = multigpu.owned_pixels(rank, world, stripe, width, height)
+    # a tile whose value encodes the global pixel index, as the renderer's resolve would produce
+    tile = torch.from_numpy(np.stack([pix, pix * 2, pix * 3], -1).astype(np.float32))
+    frame = multigpu.gather_frame(tile, width, height, stripe, dist, dst=0)
+    if rank == 0:
+        q.put(frame.numpy())
+    else:
+        assert frame is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,width,height,stripe", [(2, 16, 20, 8), (3, 7, 33, 4), (2, 5, 3, 8)])
+def test_gather_frame_gloo(world, width, height, stripe):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, width, height, stripe, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    frame = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    idx = np.arange(width * height, dtype=np.float32)
+    assert np.array_equal(frame, np.stack([idx, idx * 2, idx * 3], -1))
+
+
+@pytest.mark.parametrize("world,stripe,height", [(1, 8, 10), (2, 8, 1080), (8, 8, 1080), (8, 32, 2160), (3, 5, 17)])
+def test_partition_is_exact_cover(world, stripe, height):
+    rows = np.concatenate([multigpu.owned_rows(r, world, stripe, height) for r in range(world)])
+    assert np.array_equal(np.sort(rows), np.arange(height))
+    sizes = [multigpu.owned_rows(r, world, stripe, height).size for r in range(world)]
+    assert max(sizes) - min(sizes) <= stripe
