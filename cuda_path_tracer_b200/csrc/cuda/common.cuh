@@ -138,15 +138,19 @@ struct LbvhRef {
 };
 
 // Traversal layout derived from it (DESIGN.md "compressed node layout"): one 64-byte record per
-// internal node holding BOTH children's boxes and links, so a node visit is four coalescable
-// 16-byte loads from one 64-byte line instead of the reference's int2 + 4 scattered float4
-// (src/kernels/ray_cast.cu:78-88).  Leaves carry their three vertices inline (48 bytes), which
-// removes the primitive_indices -> indices_matid -> pos chain (:55-63).
+// internal node holding BOTH children's boxes and links, so a node visit is two 32-byte loads
+// (sm_100 LDG.256, one full sector per lane per instruction) from one 64-byte record instead of
+// the reference's int2 + 4 scattered float4 (src/kernels/ray_cast.cu:78-88).  Leaves carry their
+// three vertices inline in a 64-byte record as well (two sectors, 32-byte aligned), which removes
+// the primitive_indices -> indices_matid -> pos chain (:55-63).  RayCast is bound by the L1 data
+// pipe (wavefronts), not by bytes, so records are laid out per sector, not packed.
 //   node[4*i+0] = (left.min.xyz , bits(left link))     link >= 0 : internal node index
 //   node[4*i+1] = (left.max.xyz , bits(right link))    link <  0 : ~(sorted leaf position)
 //   node[4*i+2] = (right.min.xyz, 0)
 //   node[4*i+3] = (right.max.xyz, 0)
-//   tri[3*k+0]  = (v0.xyz, bits(triangle index)), tri[3*k+1] = (v1.xyz,0), tri[3*k+2] = (v2.xyz,0)
+//   tri[4*k+0]  = (v0.xyz, bits(triangle index)), tri[4*k+1] = (v1.xyz, bits(material id)),
+//   tri[4*k+2]  = (v2.xyz, 0),                    tri[4*k+3] = 0
+#define PTB_TRI_STRIDE 4
 struct BvhDev {
     const float4* node;
     const float4* tri;

@@ -359,9 +359,10 @@ __global__ void __launch_bounds__(256) k_pack(LbvhBuffers b, const float4* __res
         int prim = b.ref.primitive_indices[n + i];
         int4 im = __ldg(&indices_matid[prim]);
         float4 v0 = __ldg(&pos[im.x]), v1 = __ldg(&pos[im.y]), v2 = __ldg(&pos[im.z]);
-        b.tri[3 * (size_t)i + 0] = make_float4(v0.x, v0.y, v0.z, __int_as_float(prim));
-        b.tri[3 * (size_t)i + 1] = make_float4(v1.x, v1.y, v1.z, __int_as_float(im.w));
-        b.tri[3 * (size_t)i + 2] = make_float4(v2.x, v2.y, v2.z, 0.0f);
+        b.tri[PTB_TRI_STRIDE * (size_t)i + 0] = make_float4(v0.x, v0.y, v0.z, __int_as_float(prim));
+        b.tri[PTB_TRI_STRIDE * (size_t)i + 1] = make_float4(v1.x, v1.y, v1.z, __int_as_float(im.w));
+        b.tri[PTB_TRI_STRIDE * (size_t)i + 2] = make_float4(v2.x, v2.y, v2.z, 0.0f);
+        b.tri[PTB_TRI_STRIDE * (size_t)i + 3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
 }
 
@@ -391,7 +392,7 @@ int lbvh_alloc(LbvhBuffers& b, int n) {
     A(dalloc(b.ref.escape_indices, 2 * (size_t)n, t));
     A(dalloc(b.ref.world_aabb, 2, t));
     A(dalloc(b.node, 4 * (size_t)n, t));
-    A(dalloc(b.tri, 3 * (size_t)n, t));
+    A(dalloc(b.tri, PTB_TRI_STRIDE * (size_t)n, t));
     A(dalloc(b.key_a, (size_t)n, t));
     A(dalloc(b.key_b, (size_t)n, t));
     A(dalloc(b.val_b, (size_t)n, t));

@@ -10,7 +10,7 @@ struct LbvhBuffers {
     LbvhRef ref{};
     // traversal layout (see BvhDev in common.cuh)
     float4* node = nullptr;      // 4 * (N-1)
-    float4* tri = nullptr;       // 3 * N
+    float4* tri = nullptr;       // PTB_TRI_STRIDE * N
     // scratch kept for rebuilds
     unsigned int* key_a = nullptr;   // 30-bit Morton codes, ping
     unsigned int* key_b = nullptr;   // pong

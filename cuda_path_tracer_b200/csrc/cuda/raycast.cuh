@@ -4,8 +4,8 @@
 // (src/kernels/ray_cast.cu:26-107): near child first, ties go right, strict `t < t_min`, and the
 // walk stops when 32 entries are stacked.  With identical slab / triangle arithmetic this makes
 // the winning triangle, t and (u, v) bit-identical, including for equal-t ties on shared edges.
-// What changes is the memory side: one 64-byte node record per internal node (4 x LDG.128 from
-// one line, instead of int2 + 4 scattered float4), vertices inline in the leaf (3 x LDG.128,
+// What changes is the memory side: one 64-byte node record per internal node (2 x LDG.256,
+// instead of int2 + 4 scattered float4), vertices inline in the leaf (LDG.256 + LDG.128,
 // instead of primitive_indices -> indices_matid -> 3 x pos), the stack in shared memory instead of
 // local memory, and no function calls (the reference's two tests are __noinline__).
 #pragma once
@@ -56,6 +56,16 @@ __device__ __forceinline__ float triangle_test(Vec3 v0, Vec3 v1, Vec3 v2, Vec3 o
     return (t > 1e-7f) ? t : -1.0f;
 }
 
+// One 32-byte sector per lane per instruction (LDG.E.256, sm_100+): half the L1 wavefronts of two 16-byte loads.
+struct F8 { float4 a, b; };
+__device__ __forceinline__ F8 ldg256(const float4* p) {
+    F8 r;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(r.a.x), "=f"(r.a.y), "=f"(r.a.z), "=f"(r.a.w), "=f"(r.b.x), "=f"(r.b.y), "=f"(r.b.z), "=f"(r.b.w)
+        : "l"(p));
+    return r;
+}
+
 struct Hit {
     int prim;      // triangle index, -1 = miss
     int mat;       // material id of the hit triangle
@@ -72,8 +82,9 @@ __device__ __forceinline__ Hit trace_closest(const BvhDev& bvh, Vec3 o, Vec3 d, 
     while (node != PTB_NODE_NONE || sp > 0) {
         if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
         if (node < 0) {
-            const float4* tp = bvh.tri + 3 * (size_t)(~node);
-            float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
             float u, v;
             float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, u, v);
             if (t > PTB_EPSILON && t < h.t) {
@@ -84,7 +95,8 @@ __device__ __forceinline__ Hit trace_closest(const BvhDev& bvh, Vec3 o, Vec3 d, 
             node = PTB_NODE_NONE;
         } else {
             const float4* np = bvh.node + 4 * (size_t)node;
-            float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            F8 nl = ldg256(np), nr = ldg256(np + 2);
+            float4 n0 = nl.a, n1 = nl.b, n2 = nr.a, n3 = nr.b;
             float t_l = slab_test(n0, n1, o, inv);
             float t_r = slab_test(n2, n3, o, inv);
             int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
@@ -117,15 +129,17 @@ __device__ __forceinline__ int trace_any(const BvhDev& bvh, Vec3 o, Vec3 d, floa
     while (node != PTB_NODE_NONE || sp > 0) {
         if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
         if (node < 0) {
-            const float4* tp = bvh.tri + 3 * (size_t)(~node);
-            float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
             float u, v;
             float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, u, v);
             if (t > PTB_EPSILON && t < t_limit) return 1;
             node = PTB_NODE_NONE;
         } else {
             const float4* np = bvh.node + 4 * (size_t)node;
-            float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            F8 nl = ldg256(np), nr = ldg256(np + 2);
+            float4 n0 = nl.a, n1 = nl.b, n2 = nr.a, n3 = nr.b;
             float t_l = slab_test(n0, n1, o, inv);
             float t_r = slab_test(n2, n3, o, inv);
             int left = __float_as_int(n0.w), right = __float_as_int(n1.w);

@@ -2,6 +2,7 @@
 // per-frame CUDA graph, staged (parity) execution, read-backs.
 // Replaces pathtrace_wavefront::{PathtraceInit, Pathtrace, PathtraceFree} (reference
 // src/pathtrace_wavefront.cu:144-413) and WavefrontPathTracerState (src/wavefront_internal.cu).
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #include <cstring>
@@ -214,6 +215,12 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     cudaDeviceProp prop;
     TRYCU(cudaGetDeviceProperties(&prop, cfg.device));
     r->launch.num_sms = prop.multiProcessorCount;
+    {   // tuning knobs of the RayCast scheduler (defaults are the measured best; env overrides are for A/B runs only)
+        auto knob = [](const char* name, int def) { const char* e = std::getenv(name); return e ? std::atoi(e) : def; };
+        r->launch.rc_variant = knob("PTB_RC_VARIANT", 0);
+        r->launch.rc_refill = knob("PTB_RC_REFILL", 8);
+        r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
+    }
 
     FrameDev& f = r->frame;
     // ---- mesh, materials, lights (initSceneGeometry, src/wavefront_internal.cu:118-167)
