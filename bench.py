@@ -7,9 +7,11 @@ synthetic 143,173-triangle Fireplace-like room (PBR / diffuse / mirror / dielect
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
     python bench.py --impl reference ...     # the reference's own wavefront build (oracle/_ref/refdump), same scene
 
-A step = one frame: RayGen -> 8 x (RayCast, Logic, Shade) -> resolve -> (N > 1) gather of the tiles to rank 0.
-N > 1 partitions the SAME frame over the ranks (interleaved 8-row stripes, global pixel indices), so scaling is
-strong and the gathered frame is bit-identical to the 1-GPU frame.
+A step = one full frame per GPU: RayGen -> 8 x (RayCast, Logic, Shade) -> resolve.  With N > 1 the ranks take
+different sample indices of the same frame (rank r renders iterations r+1, r+1+N, ...) and one NCCL reduce per step
+adds the resolved sums on rank 0, so a step is N samples per pixel and per-GPU work is fixed ("scaling": "weak").
+The other partition north_star names -- ONE frame split into interleaved 8-row stripes, gathered to rank 0,
+bit-identical to the 1-GPU frame -- is timed in the same run and reported under config.tile_partition (strong scaling).
 """
 import argparse
 import json
@@ -171,19 +173,11 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene = ptb.Scene(make_scene(rank))
     stripe = 8
-    r = ptb.Renderer(scene, device=local_rank, rank=rank, world=world, stripe_rows=stripe)
-    stream = torch.cuda.Stream()
-    r.set_stream(stream.cuda_stream)
     W, H = RES
     P = W * H
-    tile = torch.empty((r.owned_pixels, 3), dtype=torch.float32, device="cuda")
+    stream = torch.cuda.Stream()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")     # > 126 MB L2
     host = torch.empty((P, 3), dtype=torch.float32, pin_memory=True) if rank == 0 else None
-
-    def step(it):
-        r.render(it)
-        r.resolve_device(tile.data_ptr(), it)
-        return multigpu.gather_frame(tile, W, H, stripe, dist) if world > 1 else tile
 
     def barrier():
         torch.cuda.synchronize()
@@ -191,68 +185,114 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    with torch.cuda.stream(stream):
-        for it in range(1, args.warmup + 1):
-            step(it)
-        barrier()
-        r.stats_reset()
-        clocks = ClockSampler(local_rank)
-        if rank == 0:
-            clocks.start()
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
+    def timed(step, first):
+        """W warm-up + K timed steps of `step(k)`; returns (device ms over the K steps, max over ranks)."""
+        for k in range(args.warmup):
+            step(first + k)
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         barrier()
         for k in range(args.steps):
             flush.zero_()                         # L2 flush between timed iterations (outside the event pair)
             ev[k][0].record(stream)
-            step(args.warmup + 1 + k)
+            step(first + args.warmup + k)
             ev[k][1].record(stream)
         barrier()
-        total_ms = sum(a.elapsed_time(b) for a, b in ev)
+        return allmax(sum(a.elapsed_time(b) for a, b in ev))
+
+    with torch.cuda.stream(stream):
+        # ---- N > 1, secondary figure: TILE partition of ONE frame per step (strong scaling, bit-identical to 1 GPU)
+        tile_info = None
+        if world > 1:
+            rt = ptb.Renderer(scene, device=local_rank, rank=rank, world=world, stripe_rows=stripe)
+            rt.set_stream(stream.cuda_stream)
+            fg = multigpu.FrameGather(W, H, stripe, dist, device="cuda")
+
+            def tile_step(k):
+                rt.render(k + 1)
+                rt.resolve_device(fg.tile.data_ptr(), k + 1)
+                return fg.gather()
+            tms = timed(tile_step, 0) / args.steps
+            tile_info = {"what": f"one 1080p frame per step split over {world} GPUs (interleaved {stripe}-row stripes, NCCL gather to rank 0), bit-identical to 1 GPU",
+                         "ms_per_frame": round(tms, 4), "mpaths_per_s": round(P / tms / 1e3, 3), "scaling": "strong"}
+            rt.free()
+            del fg
+        # ---- headline: every rank renders full frames; N > 1 = sample-index partition, one reduce per step
+        r = ptb.Renderer(scene, device=local_rank)
+        r.set_stream(stream.cuda_stream)
+        sr = multigpu.SampleReduce(W, H, dist, device="cuda") if world > 1 else None
+        tile = sr.sum if world > 1 else torch.empty((P, 3), dtype=torch.float32, device="cuda")
+
+        def step(k):
+            if world == 1:
+                r.render(k + 1)
+                r.resolve_device(tile.data_ptr(), k + 1)
+                return tile
+            if k == 0:
+                r.clear()
+            r.render(sr.iteration(k))
+            r.resolve_device(tile.data_ptr(), 1, capi.IMG_SUM_RGB32F)
+            return sr.reduce((k + 1) * world)
+
+        clocks = ClockSampler(local_rank)
+        for k in range(args.warmup):                 # extra warm-up so that stats_reset sits before the timed loop only
+            step(k)
+        barrier()
+        r.stats_reset()
+        if rank == 0:
+            clocks.start()
+        total_ms = timed(step, args.warmup)
         clk = clocks.stop() if rank == 0 else None
         st = r.stats()
-        t = torch.tensor([total_ms, float(st.kernel_launches + args.steps), float(st.extension_rays + st.shadow_rays)], dtype=torch.float64, device="cuda")
+        frames_counted = args.steps + args.warmup
+        t = torch.tensor([float(st.kernel_launches), float(st.extension_rays + st.shadow_rays)], dtype=torch.float64, device="cuda")
         if world > 1:
-            tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-            tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-            total_ms, launches, rays = float(tmax[0]), int(tsum[1]), float(tsum[2])
-        else:
-            launches, rays = int(t[1]), float(t[2])
-        # ---- end to end through the public API with HOST buffers: render + resolve + (gather) + D2H of the frame, every step
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        launches = int(float(t[0]) * args.steps / frames_counted)          # stats cover warm-up + timed steps of timed()
+        rays = float(t[1]) * args.steps / frames_counted
+        # ---- end to end through the public API with HOST buffers: render + resolve (+ reduce) + D2H of the frame, every step
         barrier()
         t0 = time.perf_counter()
         for k in range(args.steps):
-            it = args.warmup + args.steps + 1 + k
+            kk = 2 * args.warmup + args.steps + k
             if world == 1:
-                r.render(it)
-                r.resolve(it, out=host.numpy())           # ptb_resolve to a host pointer: kernel + D2H + sync inside
+                r.render(kk + 1)
+                r.resolve(kk + 1, out=host.numpy())           # ptb_resolve to a host pointer: kernel + D2H + sync inside
             else:
-                frame = step(it)
+                frame = step(kk)
                 if rank == 0:
                     host.copy_(frame, non_blocking=True)
                 torch.cuda.synchronize()
         barrier()
-        e2e_s = time.perf_counter() - t0
-        if world > 1:
-            te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-            e2e_s = float(te[0])
+        e2e_s = allmax(time.perf_counter() - t0)
         roof = cpu = None
         if not args.no_extras:
-            roof, cpu = roofline_and_cpu(r, scene, world, rank, rays / (args.steps * P))
+            roof, cpu = roofline_and_cpu(r, scene, world, rank, rays / (args.steps * P * world))
+    paths_per_step = P * world
     if rank == 0:
         ms = total_ms / args.steps
-        out = {"metric": "Mpaths/s", "value": round(P / ms / 1e3, 3), "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-               "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-               "config": {"workload": WORKLOAD, "partition": f"{world} x interleaved {stripe}-row stripes, scene+LBVH replicated, 1 gather/frame" if world > 1 else "single GPU",
+        part = "single GPU" if world == 1 else (f"sample-index partition: each of the {world} GPUs renders a full 1080p frame per step (iterations rank+1, rank+1+N, ...), "
+                                                f"scene+LBVH replicated, ONE NCCL reduce of the resolved sums to rank 0 per step; a step is {world} spp")
+        out = {"metric": "Mpaths/s", "value": round(paths_per_step / ms / 1e3, 3), "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": WORKLOAD, "partition": part, "paths_per_step": paths_per_step,
                           "l2": "256 MB flush write between timed steps", "timing": "CUDA events on the launching stream per step, max over ranks",
-                          "mrays_per_s": round(rays / (total_ms * 1e-3) / 1e6, 1), "rays_per_path": round(rays / (args.steps * P), 3),
+                          "mrays_per_s": round(rays / (total_ms * 1e-3) / 1e6, 1), "rays_per_path": round(rays / (args.steps * paths_per_step), 3),
                           "lbvh_build_ms": round(st.lbvh_build_ms, 4), "lbvh_max_depth": st.lbvh_max_depth, "parity": "radiance bit-exact vs reference (tests/test_gpu_parity.py)"},
                "gpu_launches": launches, "clocks": clk,
-               "e2e": {"value": round(args.steps * P / e2e_s / 1e6, 3), "unit": "Mpaths/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": P * 12,
-                       "note": "ptb_render + ptb_resolve into a pinned HOST buffer every step (wall clock incl. sync); the scene is static, the only per-step input is the iteration index"},
+               "e2e": {"value": round(args.steps * paths_per_step / e2e_s / 1e6, 3), "unit": "Mpaths/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": P * 12,
+                       "note": "ptb_render + ptb_resolve (+ reduce) into a pinned HOST buffer every step (wall clock incl. sync); the scene is static, the only per-step input is the iteration index"},
                "roofline": roof}
         if cpu is not None:
             out["cpu_baseline"] = cpu
+        if tile_info is not None:
+            out["config"]["tile_partition"] = tile_info
         print(json.dumps(out))
     r.free()
     if world > 1:

@@ -83,6 +83,7 @@ SIGNATURES = {
     "ptb_free": (C.c_int, [P]),
     "ptb_render": (C.c_int, [P, C.c_int32]),
     "ptb_render_many": (C.c_int, [P, C.c_int32, C.c_int32]),
+    "ptb_clear_accumulators": (C.c_int, [P]),
     "ptb_sync": (C.c_int, [P]),
     "ptb_set_stream": (C.c_int, [P, P]),
     "ptb_resolve": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32]),

@@ -395,6 +395,14 @@ int ptb_render_many(ptb_renderer* r, int32_t first, int32_t count) {
 
 int ptb_render(ptb_renderer* r, int32_t iteration) { return ptb_render_many(r, iteration, 1); }
 
+int ptb_clear_accumulators(ptb_renderer* r) {
+    if (!r) return fail(PTB_ERR_INVALID, "ptb_clear_accumulators: null renderer");
+    CU(cudaSetDevice(r->device));
+    r->kernel_launches += launch_clear_accumulators(r->frame, r->stream);
+    CU(cudaGetLastError());
+    return PTB_OK;
+}
+
 int ptb_resolve(ptb_renderer* r, void* dst, int32_t format, int32_t iteration, int32_t dst_on_device) {
     if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_resolve: null argument");
     if (format < PTB_IMG_SUM_RGB32F || format > PTB_IMG_RGBA8) return fail(PTB_ERR_INVALID, "ptb_resolve: unknown format");

@@ -21,27 +21,87 @@ def owned_pixels(rank, world, stripe_rows, width, height):
     return (rows[:, None] * width + np.arange(width)[None, :]).reshape(-1)
 
 
+class FrameGather:
+    """Per-frame gather of the ranks' tiles into the full frame on rank `dst`, with every buffer and
+    index allocated once.  `send` ([pad, C], pad = largest tile) is the buffer a rank resolves its tile
+    into (rows beyond its own tile are padding); `gather()` issues ONE collective and, on `dst`, places
+    the stripes at their global rows: a strided copy per rank when the stripes are whole, an index copy
+    otherwise."""
+
+    def __init__(self, width, height, stripe_rows, dist, channels=3, dtype=None, device="cpu", dst=0):
+        import torch
+        self.dist, self.dst = dist, dst
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.width, self.height, self.stripe = width, height, stripe_rows
+        dtype = dtype or torch.float32
+        self.counts = [owned_rows(r, self.world, stripe_rows, height).size * width for r in range(self.world)]
+        self.owned = self.counts[self.rank]
+        pad = max(self.counts)
+        self.send = torch.zeros((pad, channels), dtype=dtype, device=device)
+        self.recv = self.frame = self.index = None
+        self.whole = height % stripe_rows == 0
+        if self.rank == dst:
+            self.recv = [torch.empty_like(self.send) for _ in range(self.world)]
+            self.frame = torch.empty((height * width, channels), dtype=dtype, device=device)
+            if not self.whole:
+                self.index = [torch.from_numpy(owned_pixels(r, self.world, stripe_rows, width, height)).to(device) for r in range(self.world)]
+
+    @property
+    def tile(self):
+        """View of `send` that holds exactly this rank's pixels."""
+        return self.send[:self.owned]
+
+    def gather(self):
+        if self.world == 1:
+            return self.tile
+        self.dist.gather(self.send, self.recv, dst=self.dst)
+        if self.rank != self.dst:
+            return None
+        if self.whole:
+            per = self.stripe * self.width
+            stripes = self.frame.view(self.height // self.stripe, per, -1)
+            for r in range(self.world):
+                stripes[r::self.world].copy_(self.recv[r][:self.counts[r]].view(-1, per, stripes.shape[-1]))
+        else:
+            for r in range(self.world):
+                self.frame[self.index[r]] = self.recv[r][:self.counts[r]]
+        return self.frame
+
+
 def gather_frame(local_tile, width, height, stripe_rows, dist, dst=0):
-    """Gather every rank's resolved tile (torch tensor [owned_pixels, C]) to rank `dst` and place the
-    rows at their global position.  Returns the [height*width, C] frame on `dst`, None elsewhere.
-    Tiles differ in size by at most one stripe, so they are padded to a common length for all_gather
-    -- one collective per frame."""
-    import torch
-    world, rank = dist.get_world_size(), dist.get_rank()
-    if world == 1:
+    """One-shot form: gather every rank's resolved tile (torch tensor [owned_pixels, C]) to rank `dst`.
+    Returns the [height*width, C] frame on `dst`, None elsewhere.  (Loops should keep a FrameGather.)"""
+    if dist.get_world_size() == 1:
         return local_tile
-    counts = [owned_rows(r, world, stripe_rows, height).size * width for r in range(world)]
-    pad = max(counts)
-    buf = local_tile
-    if local_tile.shape[0] != pad:
-        buf = torch.zeros((pad,) + tuple(local_tile.shape[1:]), dtype=local_tile.dtype, device=local_tile.device)
-        buf[:local_tile.shape[0]] = local_tile
-    out = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
-    dist.gather(buf, out, dst=dst)
-    if rank != dst:
-        return None
-    frame = torch.empty((height * width,) + tuple(local_tile.shape[1:]), dtype=local_tile.dtype, device=local_tile.device)
-    for r in range(world):
-        idx = torch.from_numpy(owned_pixels(r, world, stripe_rows, width, height)).to(frame.device)
-        frame[idx] = out[r][:counts[r]]
-    return frame
+    g = FrameGather(width, height, stripe_rows, dist, channels=local_tile.shape[1], dtype=local_tile.dtype,
+                    device=local_tile.device, dst=dst)
+    g.tile.copy_(local_tile)
+    return g.gather()
+
+
+class SampleReduce:
+    """Sample-index partition (north_star's second mode): every rank renders the FULL frame,
+    rank r taking iterations r+1, r+1+world, ...  -- the seeds depend only on (pixel, iteration), so the union
+    of the ranks' samples is exactly the sample set of a 1-GPU render of the same iterations.  Per displayed
+    frame the ranks' accumulated sums are added (ONE reduce to `dst`) and divided by the total sample count.
+    Unlike the tile partition this changes the order in which a pixel's samples are summed, so it agrees with
+    the 1-GPU render to float rounding (tests: <= 1e-6 relative), not bit for bit; in exchange every GPU keeps
+    full-size queues, which is what scales when the frame is small."""
+
+    def __init__(self, width, height, dist, channels=3, dtype=None, device="cpu", dst=0):
+        import torch
+        self.dist, self.dst = dist, dst
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.sum = torch.zeros((height * width, channels), dtype=dtype or torch.float32, device=device)
+
+    def iteration(self, step):
+        """1-based iteration this rank renders at 0-based step `step`."""
+        return step * self.world + self.rank + 1
+
+    def reduce(self, total_samples):
+        """`self.sum` holds this rank's resolved SUM image; returns the mean frame on `dst`, None elsewhere."""
+        if self.world > 1:
+            self.dist.reduce(self.sum, dst=self.dst, op=self.dist.ReduceOp.SUM)
+            if self.rank != self.dst:
+                return None
+        return self.sum.div_(float(total_samples))

@@ -123,6 +123,10 @@ class Renderer:
     def render(self, iteration, count=1):
         check(lib.ptb_render_many(self._h, iteration, count))
 
+    def clear(self):
+        """Zero the accumulators (what iteration 1 does implicitly); for sample-index partitions."""
+        check(lib.ptb_clear_accumulators(self._h))
+
     def sync(self):
         check(lib.ptb_sync(self._h))
 

@@ -152,6 +152,10 @@ int ptb_free(ptb_renderer* r);
 int ptb_render(ptb_renderer* r, int32_t iteration);
 /* Same as calling ptb_render for iteration = first .. first+count-1. */
 int ptb_render_many(ptb_renderer* r, int32_t first_iteration, int32_t count);
+/* Zero the direct / indirect accumulators without rendering: what iteration == 1 does implicitly
+ * (src/pathtrace_wavefront.cu:232-242), for callers that start at another iteration -- a rank of a
+ * sample-index partition renders iterations rank+1, rank+1+world, ... and never sees iteration 1. */
+int ptb_clear_accumulators(ptb_renderer* r);
 /* Wait for everything enqueued on the renderer's stream; reports deferred CUDA errors. */
 int ptb_sync(ptb_renderer* r);
 /* Use a caller-owned CUDA stream (cudaStream_t passed as void*) instead of the internal one. */

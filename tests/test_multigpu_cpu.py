@@ -35,7 +35,7 @@ def _worker(rank, world, port, width, height, stripe, q):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,width,height,stripe", [(2, 16, 20, 8), (3, 7, 33, 4), (2, 5, 3, 8)])
+@pytest.mark.parametrize("world,width,height,stripe", [(2, 16, 20, 8), (3, 7, 33, 4), (2, 5, 3, 8), (2, 16, 32, 8), (3, 6, 28, 4)])
 def test_gather_frame_gloo(world, width, height, stripe):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -57,3 +57,38 @@ def test_partition_is_exact_cover(world, stripe, height):
     assert np.array_equal(np.sort(rows), np.arange(height))
     sizes = [multigpu.owned_rows(r, world, stripe, height).size for r in range(world)]
     assert max(sizes) - min(sizes) <= stripe
+
+
+def _reduce_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sr = multigpu.SampleReduce(4, 3, dist)
+    its = [sr.iteration(k) for k in range(3)]
+    # this rank's "resolved sum" after 3 steps: the sum of its iteration numbers in every channel
+    sr.sum.fill_(float(sum(its)))
+    frame = sr.reduce(3 * world)
+    if rank == 0:
+        q.put((its, frame.numpy()))
+    else:
+        assert frame is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sample_reduce_gloo(world):
+    """Sample-index partition: the ranks' iterations tile 1..3*world exactly and the reduced frame is the mean."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_reduce_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    its, frame = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert its == [1, 1 + world, 1 + 2 * world]
+    n = 3 * world
+    assert np.allclose(frame, (n * (n + 1) / 2) / n) and frame.shape == (12, 3)
