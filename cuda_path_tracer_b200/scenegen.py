@@ -322,3 +322,160 @@ def stress_materials():
 
 def stress_camera(res=(1920, 1080)):
     return dict(resolution=res, fovy=50.0, eye=[0.0, 14.0, 38.0], look_at=[0.0, 2.0, 0.0], up=[0.0, 1.0, 0.0])
+
+
+# ------------------------------------------------------------------------------------ config 3
+def cylinder(base, radius, height, slices, stacks):
+    """Open cylinder along +y, 2*slices*stacks triangles, seam duplicated so that u runs 0..1."""
+    base = np.asarray(base, np.float64)
+    a, t = np.meshgrid(np.linspace(0, 2 * np.pi, slices + 1), np.linspace(0, 1, stacks + 1), indexing="ij")
+    n = np.stack([np.cos(a), np.zeros_like(a), np.sin(a)], -1)
+    p = base + radius * n + np.stack([np.zeros_like(t), t * height, np.zeros_like(t)], -1)
+    idx = np.arange((slices + 1) * (stacks + 1)).reshape(slices + 1, stacks + 1)
+    q0, q1, q2, q3 = idx[:-1, :-1], idx[1:, :-1], idx[1:, 1:], idx[:-1, 1:]
+    tris = np.concatenate([np.stack([q0, q2, q1], -1).reshape(-1, 3), np.stack([q0, q3, q2], -1).reshape(-1, 3)])
+    uv = np.stack([a / (2 * np.pi) * 3.0, t * 4.0], -1).reshape(-1, 2)
+    return p.reshape(-1, 3), n.reshape(-1, 3), uv, tris
+
+
+def vault(x0, x1, z, radius, y0, nu, nv):
+    """Half-cylinder arch spanning x0..x1 at depth z..z+1.2, facing down (normals toward the axis)."""
+    a, s = np.meshgrid(np.linspace(0, np.pi, nu + 1), np.linspace(0, 1, nv + 1), indexing="ij")
+    cx = 0.5 * (x0 + x1)
+    n = -np.stack([np.cos(a), np.sin(a), np.zeros_like(a)], -1)
+    p = np.stack([cx + radius * np.cos(a), y0 + radius * np.sin(a), z + 1.2 * s], -1)
+    idx = np.arange((nu + 1) * (nv + 1)).reshape(nu + 1, nv + 1)
+    q0, q1, q2, q3 = idx[:-1, :-1], idx[1:, :-1], idx[1:, 1:], idx[:-1, 1:]
+    tris = np.concatenate([np.stack([q0, q1, q2], -1).reshape(-1, 3), np.stack([q0, q2, q3], -1).reshape(-1, 3)])
+    uv = np.stack([a / np.pi * 2.0, s], -1).reshape(-1, 2)
+    return p.reshape(-1, 3), n.reshape(-1, 3), uv, tris
+
+
+def _noise(size, seed, octaves=4):
+    """Tileable value noise in [0,1] (sum of random-phase sinusoid products; deterministic)."""
+    rng = np.random.RandomState(seed)
+    y, x = np.meshgrid(np.linspace(0, 2 * np.pi, size, endpoint=False), np.linspace(0, 2 * np.pi, size, endpoint=False), indexing="ij")
+    h = np.zeros((size, size))
+    for o in range(octaves):
+        for _ in range(3):
+            fx, fy = rng.randint(1, 4 << o, 2)
+            h += np.sin(fx * x + rng.uniform(0, 6.28)) * np.cos(fy * y + rng.uniform(0, 6.28)) / (1 << o)
+    h -= h.min()
+    return h / h.max()
+
+
+def _normal_map(height, strength):
+    gx = (np.roll(height, -1, 1) - np.roll(height, 1, 1)) * strength
+    gy = (np.roll(height, -1, 0) - np.roll(height, 1, 0)) * strength
+    n = np.stack([-gx, -gy, np.ones_like(gx)], -1)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    return np.clip((n * 0.5 + 0.5) * 255, 0, 255).astype(np.uint8)
+
+
+def _texture_set(out_dir, name, size, seed, tint, pattern):
+    """diffuse / normal / metallic-roughness BMPs for one surface; returns the three file names."""
+    h = _noise(size, seed)
+    yy, xx = np.mgrid[0:size, 0:size]
+    if pattern == "brick":
+        row = (yy * 16 // size)
+        mortar = ((yy * 16 % size) < size // 40) | ((((xx + (row % 2) * size // 16) * 8) % size) < size // 40)
+        h = np.where(mortar, 0.15, 0.55 + 0.45 * h)
+    elif pattern == "tile":
+        mortar = ((yy * 8 % size) < size // 64) | ((xx * 8 % size) < size // 64)
+        h = np.where(mortar, 0.1, 0.6 + 0.4 * h * (((yy * 8 // size) + (xx * 8 // size)) % 2 * 0.5 + 0.5))
+    elif pattern == "cloth":
+        h = 0.5 + 0.25 * np.sin(xx * 2 * np.pi * 64 / size) * np.sin(yy * 2 * np.pi * 64 / size) + 0.25 * h
+    col = np.clip(np.asarray(tint)[None, None, :] * (0.35 + 0.65 * h[..., None]) * 255, 0, 255).astype(np.uint8)
+    files = [f"{name}_diffuse.bmp", f"{name}_normal.bmp", f"{name}_rough.bmp"]
+    write_bmp(os.path.join(out_dir, files[0]), col)
+    write_bmp(os.path.join(out_dir, files[1]), _normal_map(h, 6.0))
+    mr = np.zeros((size, size, 3), np.uint8)
+    mr[..., 1] = np.clip((0.35 + 0.6 * _noise(size, seed + 100, 3)) * 255, 0, 255)   # roughness factor (green)
+    mr[..., 2] = np.clip((pattern == "tile") * 0.5 * 255 * _noise(size, seed + 200, 2), 0, 255)   # metallic factor (blue)
+    write_bmp(os.path.join(out_dir, files[2]), mr)
+    return files
+
+
+def sky_hdr(path, width=2048, height=1024, sun_dir=(0.35, 0.8, 0.45), sun_radiance=4000.0):
+    """Equirect RGB32F sky: horizon-to-zenith gradient + a small bright sun (exercises the alias table and the
+    pdf-map MIS of src/kernels/logic.cu:76-103)."""
+    v, u = np.meshgrid((np.arange(height) + 0.5) / height, (np.arange(width) + 0.5) / width, indexing="ij")
+    theta, phi = v * np.pi, u * 2 * np.pi
+    d = np.stack([np.sin(theta) * np.cos(phi), np.cos(theta), np.sin(theta) * np.sin(phi)], -1)
+    up = np.clip(d[..., 1], 0, 1)
+    sky = np.stack([0.35 + 0.25 * (1 - up), 0.5 + 0.2 * (1 - up), 0.9 * np.ones_like(up)], -1) * (0.6 + 0.8 * up[..., None])
+    sky = np.where(d[..., 1:2] < 0, np.array([0.12, 0.1, 0.08]), sky)
+    s = np.asarray(sun_dir, np.float64)
+    s /= np.linalg.norm(s)
+    cosang = (d * s).sum(-1)
+    sky = sky + (cosang > np.cos(np.radians(1.5)))[..., None] * np.array([1.0, 0.93, 0.8]) * sun_radiance
+    write_hdr(path, sky.astype(np.float32))
+
+
+SPONZA_TRIANGLES = 262279
+
+
+def sponza(out_dir, res=(1920, 1080), depth=8, scale=1.0, tex_size=1024):
+    """262,279-triangle atrium (README.md:115 quotes Sponza at that size): textured floor / walls / columns /
+    arches / drapes through OBJ + MTL (map_Kd, map_bump, map_Pr => bindless textures), emissive lanterns (Ke),
+    open roof under an HDR sky with a sun.  scale < 1 shrinks the tessellation; the count is exact at scale 1."""
+    os.makedirs(out_dir, exist_ok=True)
+    q = lambda v: max(2, int(round(v * scale)))
+    sets = {"floor": ("tile", [0.8, 0.75, 0.7], 11), "wall": ("brick", [0.75, 0.45, 0.35], 12), "column": ("noise", [0.85, 0.82, 0.75], 13),
+            "arch": ("brick", [0.7, 0.68, 0.6], 14), "drape_red": ("cloth", [0.75, 0.12, 0.1], 15), "drape_blue": ("cloth", [0.15, 0.25, 0.7], 16)}
+    mtl, tex_count = [], 0
+    for name, (pattern, tint, seed) in sets.items():
+        f = _texture_set(out_dir, name, tex_size, seed, tint, pattern)
+        use = 3 if name in ("floor", "wall", "column") else 2        # 3+3+3+2+2+2 = 15 textures (+ env, + pdf map)
+        tex_count += use
+        mtl += [f"newmtl {name}", "Kd 0.9 0.9 0.9", "Ks 0.04 0.04 0.04", "Ns 400", "Ni 1.0", "d 1.0", "illum 2", f"map_Kd {f[0]}", f"map_bump {f[1]}"]
+        if use == 3:
+            mtl.append(f"map_Pr {f[2]}")
+        mtl.append("")
+    mtl += ["newmtl plaster", "Kd 0.8 0.78 0.7", "Ks 0 0 0", "Ns 10", "Ni 1.0", "d 1.0", "illum 2", "",
+            "newmtl lantern", "Kd 1 1 1", "Ke 30 24 15", "Ks 0 0 0", "Ns 10", "Ni 1.0", "d 1.0", "illum 2", ""]
+    with open(os.path.join(out_dir, "atrium.mtl"), "w") as fh:
+        fh.write("\n".join(mtl))
+    objs, total = [], [0]
+
+    def add(name, part, material):
+        names = material if isinstance(material, list) else [material] * len(part[3])
+        write_obj(os.path.join(out_dir, name + ".obj"), *part, mtllib="atrium.mtl", usemtl=names, with_uv=True)
+        objs.append(_obj_entry(os.path.join(out_dir, name + ".obj")))
+        total[0] += len(part[3])
+
+    X, Y, Z = 6.0, 9.0, 16.0
+    g = q(160)
+    add("floor", grid([-X, 0, -Z], [2 * X, 0, 0], [0, 0, 2 * Z], g, g, [0, 1, 0], 0.02, 21), "floor")
+    add("wall_left", grid([-X, 0, -Z], [0, 0, 2 * Z], [0, Y, 0], g, q(60), [1, 0, 0], 0.05, 22), "wall")
+    add("wall_right", grid([X, 0, -Z], [0, 0, 2 * Z], [0, Y, 0], g, q(60), [-1, 0, 0], 0.05, 23), "wall")
+    add("wall_back", grid([-X, 0, -Z], [2 * X, 0, 0], [0, Y, 0], q(80), q(60), [0, 0, 1], 0.05, 24), "wall")
+    add("wall_front", grid([-X, 0, Z], [2 * X, 0, 0], [0, Y, 0], q(80), q(60), [0, 0, -1], 0.05, 25), "plaster")
+    cols, arches = [], []
+    for k in range(10):
+        z = -Z + 1.6 + k * (2 * Z - 3.2) / 9
+        for x in (-3.4, 3.4):
+            cols.append(cylinder([x, 0, z], 0.45, 5.0, q(48), q(40)))
+        arches.append(vault(-3.4, 3.4, z - 0.6, 3.4, 5.0, q(48), q(24)))
+    add("columns", merge(cols), "column")
+    add("arches", merge(arches), "arch")
+    drapes, names = [], []
+    for k in range(6):
+        z = -Z + 3.0 + k * 5.0
+        x = -X + 0.35 if k % 2 == 0 else X - 0.35
+        nrm = [1, 0, 0] if k % 2 == 0 else [-1, 0, 0]
+        d = grid([x, 2.0, z], [0, 0, 2.4], [0, 5.0, 0], q(60), q(50), nrm, 0.12, 30 + k)
+        drapes.append(d)
+        names += ["drape_red" if k % 3 else "drape_blue"] * len(d[3])
+    add("drapes", merge(drapes), names)           # one OBJ, two MTL materials: exercises the usemtl switch
+    lanterns = [box([x - 0.15, 4.2, z - 0.15], [x + 0.15, 4.5, z + 0.15]) for x in (-2.0, 2.0) for z in (-8.0, 8.0)]
+    add("lanterns", merge(lanterns), "lantern")
+    if scale == 1.0:
+        add("trim", ribbon([-X + 0.1, 0.05, -Z + 0.05], [0.0013, 0, 0], [0, 0.15, 0], [0, 0, 1], SPONZA_TRIANGLES - total[0]), "plaster")
+        assert total[0] == SPONZA_TRIANGLES, total[0]
+    sky_hdr(os.path.join(out_dir, "sky.hdr"), 2048 if scale == 1.0 else 512, 1024 if scale == 1.0 else 256)
+    cam = {"RES": list(res), "FOVY": 60.0, "ITERATIONS": 16, "DEPTH": depth, "FILE": "atrium",
+           "EYE": [0.4, 2.4, 13.5], "LOOKAT": [-0.3, 3.2, -4.0], "UP": [0.0, 1.0, 0.0]}
+    path = os.path.join(out_dir, "scene.json")
+    write_scene(path, cam, {}, objs, env=os.path.join(out_dir, "sky.hdr"))
+    return path, total[0]

@@ -26,6 +26,16 @@ def fire_small(tmp_path_factory):
 
 
 @pytest.fixture(scope="module")
+def sponza_small(tmp_path_factory):
+    return scenegen.sponza(str(tmp_path_factory.mktemp("sponza_small")), res=(320, 180), scale=0.2, tex_size=128)[0]
+
+
+@pytest.fixture(scope="module")
+def sponza_full(tmp_path_factory):
+    return scenegen.sponza(str(tmp_path_factory.mktemp("sponza_full")), res=(1920, 1080))[0]
+
+
+@pytest.fixture(scope="module")
 def fire_full(tmp_path_factory):
     return scenegen.fireplace(str(tmp_path_factory.mktemp("fire_full")), res=(1920, 1080))[0]
 
@@ -109,12 +119,13 @@ def _need_ref():
         pytest.skip("oracle/_ref/refdump not present (built only where /root/reference exists)")
 
 
-@pytest.mark.parametrize("which", ["cornell", "fire_small"])
-def test_staged_frame_vs_reference(which, fire_small, tmp_path):
+@pytest.mark.parametrize("which", ["cornell", "fire_small", "sponza_small"])
+def test_staged_frame_vs_reference(which, fire_small, sponza_small, tmp_path):
     """Every stage of every bounce against the unmodified reference: queue counters equal, queue
     contents equal as sets, path state / shadow queue / accumulators bit-equal."""
     _need_ref()
-    scene_json = scenegen.cornell(str(tmp_path / "c"), res=(200, 160)) if which == "cornell" else fire_small
+    scene_json = {"cornell": lambda: scenegen.cornell(str(tmp_path / "c"), res=(200, 160)), "fire_small": lambda: fire_small,
+                  "sponza_small": lambda: sponza_small}[which]()        # sponza: MTL materials, textures, normal maps, HDR env + pdf-map MIS
     d = str(tmp_path / "ref")
     log = par.run_refdump(scene_json, d, iters=2, stages=True, selfcheck=True)
     assert '"mismatching_floats": 0' in log
@@ -144,6 +155,24 @@ def test_radiance_vs_reference_full_size(fire_full, tmp_path):
     rr = par.radiance_report(ref.load("direct", "<f4", 3), ref.load("indirect", "<f4", 3), dn, inn, 3)
     assert rr["max_rel_err"] <= 1e-4 and rr["rmse"] <= 1e-3, rr       # north_star tolerance
     assert rr["bit_mismatch_direct"] == 0 and rr["bit_mismatch_indirect"] == 0, rr   # what is actually met
+    r.free()
+
+
+def test_radiance_vs_reference_262k_textured(sponza_full, tmp_path):
+    """BASELINE config[2]: 262,279 triangles, 15 bindless textures, HDR sky with alias/pdf map, 1920x1080, 8 bounces; 2 spp."""
+    _need_ref()
+    d = str(tmp_path / "ref")
+    par.run_refdump(sponza_full, d, iters=2, stages=False)
+    ref = par.RefDump(d)
+    s = ptb.Scene(sponza_full)
+    assert all(par.compare_scene(ref, s).values())
+    r = ptb.Renderer(s)
+    assert all(par.compare_lbvh(ref, r).values())
+    r.render(1, 2)
+    dn, inn = r.accumulators()
+    rr = par.radiance_report(ref.load("direct", "<f4", 3), ref.load("indirect", "<f4", 3), dn, inn, 2)
+    assert rr["max_rel_err"] <= 1e-4 and rr["rmse"] <= 1e-3, rr       # north_star tolerance
+    assert rr["bit_mismatch_direct"] == 0 and rr["bit_mismatch_indirect"] == 0, rr
     r.free()
 
 
