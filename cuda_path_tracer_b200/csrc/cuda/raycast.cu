@@ -7,6 +7,11 @@
 
 namespace ptb {
 
+#define PTB_SH_MINBLOCKS 12   /* any-hit keeps no hit record: 40 registers without spills, 48 resident warps per SM */
+#ifndef PTB_RC_MINBLOCKS
+#define PTB_RC_MINBLOCKS 10
+#endif
+
 // one 32-ray batch per warp fetch
 __device__ __forceinline__ int warp_fetch(int* cursor) {
     int base = 0;
@@ -14,7 +19,7 @@ __device__ __forceinline__ int warp_fetch(int* cursor) {
     return __shfl_sync(0xffffffffu, base, 0);
 }
 
-__global__ void __launch_bounds__(PTB_RC_THREADS) k_trace_extension(FrameDev f, int bounce, int* cursor) {
+__global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_extension(FrameDev f, int bounce, int* cursor) {
     __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
     const int count = f.ctr[bounce * CTR_STRIDE + CTR_EXT];
     int* my_stack = stack + threadIdx.x;
@@ -174,7 +179,7 @@ __global__ void __launch_bounds__(PTB_RC_THREADS) k_batch_closest_pl(BvhDev bvh,
 }
 
 template <int STACK, bool SHARED>
-__global__ void __launch_bounds__(PTB_RC_THREADS) k_trace_shadow(FrameDev f, int bounce) {
+__global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_SH_MINBLOCKS : 1) k_trace_shadow(FrameDev f, int bounce) {
     __shared__ int sstack[SHARED ? STACK * PTB_RC_THREADS : 1];
     int lstack[SHARED ? 1 : STACK];
     int* my_stack = SHARED ? (sstack + threadIdx.x) : lstack;
@@ -216,8 +221,12 @@ int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, cons
 int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
     run_extension(f, bounce, f.ctr + bounce * CTR_STRIDE + CTR_WORK_EXT, c, s);
     if (bounce == 0) return 1;   // no shadow rays exist before the first Shade (counter zeroed by RayGen, src/kernels/ray_gen.cu:121-124)
-    if (c.shadow_deep) k_trace_shadow<256, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce);
-    else k_trace_shadow<PTB_SHADOW_STACK, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce);
+    // the DFS stack never holds more than one entry per tree level: size it from the measured LBVH depth
+    const int g = rc_grid(c);
+    if (c.shadow_deep == 3) k_trace_shadow<256, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (c.shadow_deep == 0) k_trace_shadow<32, true><<<c.num_sms * PTB_SH_MINBLOCKS, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (c.shadow_deep == 1) k_trace_shadow<48, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else k_trace_shadow<64, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
     return 2;
 }
 
@@ -267,7 +276,7 @@ int launch_trace_batch_closest(const BvhDev& bvh, const float4* ori, const float
 int launch_trace_batch_occluded(const BvhDev& bvh, const float4* ori_tmax, const float4* dir, int n, int* occluded, int* work,
                                 int* error_flag, const LaunchCfg& c, cudaStream_t s) {
     cudaMemsetAsync(work, 0, sizeof(int), s);
-    if (c.shadow_deep) k_batch_occluded<256, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(bvh, ori_tmax, dir, n, occluded, work, error_flag);
+    if (c.shadow_deep == 3) k_batch_occluded<256, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(bvh, ori_tmax, dir, n, occluded, work, error_flag);
     else k_batch_occluded<PTB_SHADOW_STACK, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(bvh, ori_tmax, dir, n, occluded, work, error_flag);
     return 1;
 }

@@ -279,7 +279,9 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         f.bvh.root_max = root[1];
         f.bvh.num_triangles = N;
         if (r->lbvh_max_depth > 256) { ptb_free(r); return fail(PTB_ERR_UNSUPPORTED, "ptb_init: LBVH deeper than 256 levels"); }
-        r->launch.shadow_deep = r->lbvh_max_depth > 64 ? 1 : 0;
+        // any-hit stack: at most one entry per internal node on the root-to-leaf path, i.e. <= lbvh_max_depth
+        const int dmax = r->lbvh_max_depth;
+        r->launch.shadow_deep = dmax <= 32 ? 0 : dmax <= 48 ? 1 : dmax <= 64 ? 2 : 3;
     }
 
     // ---- path pool, queues, accumulators (initWavefrontQueues / initImageSystem,

@@ -13,7 +13,7 @@ from cuda_path_tracer_b200 import capi, scenegen
 configs = [dict(PTB_RC_VARIANT=0)] + [dict(PTB_RC_VARIANT=1, PTB_RC_REFILL=r, PTB_RC_BLOCKS=b) for r, b in
                                         [(1, 8), (4, 8), (8, 8), (16, 8), (24, 8), (32, 8), (8, 10), (16, 10)]]
 if len(sys.argv) > 1:
-    configs = [dict(kv.split("=") for kv in a.split(",")) for a in sys.argv[1:]]
+    configs = [dict(kv.split("=") for kv in a.split(",") if kv) for a in sys.argv[1:]]
 scene = ptb.Scene(scenegen.fireplace("/tmp/rc_ab_fire", res=(1920, 1080))[0])
 base = None
 for cfg in configs:
