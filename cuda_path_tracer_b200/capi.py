@@ -61,7 +61,7 @@ class TileInfo(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("extension_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("frames", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("lbvh_build_ms", C.c_float), ("lbvh_max_depth", C.c_int32),
-                ("num_triangles", C.c_int32), ("reserved", C.c_int32)]
+                ("num_triangles", C.c_int32), ("last_batch_ms", C.c_float)]
 
 
 # name -> (restype, argtypes); the list doubles as the symbol inventory the CPU test checks

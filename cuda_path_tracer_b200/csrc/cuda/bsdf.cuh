@@ -12,29 +12,13 @@
 // reproduces those boundaries; everything they call is inlined, as it is in the reference build.
 #pragma once
 #include "common.cuh"
+#include "material.cuh"
 
 #define PTB_BSDF_ENTRY static __device__ __noinline__
 
 namespace ptb {
 
 struct Vec2 { float x, y; };
-
-struct Mat {          // `Material`, src/scene_structs.h:52-65
-    Vec3 basecolor;
-    float metallic, roughness, emittance, ior;
-    int type, diffuse_tex, normal_tex, mr_tex;
-};
-
-static __device__ Mat load_material(const ptb_material* __restrict__ mats, int id) {
-    const float4* p = reinterpret_cast<const float4*>(mats + id);
-    float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-    Mat m;
-    m.basecolor = Vec3(a.x, a.y, a.z);
-    m.metallic = a.w;
-    m.roughness = b.x; m.emittance = b.y; m.ior = b.z; m.type = __float_as_int(b.w);
-    m.diffuse_tex = __float_as_int(c.x); m.normal_tex = __float_as_int(c.y); m.mr_tex = __float_as_int(c.z);
-    return m;
-}
 
 // LocalToWorld, src/interactions.cu:6-15
 static __device__ Vec3 local_to_world(V3R l, V3R N) {
@@ -264,13 +248,6 @@ PTB_BSDF_ENTRY void sample_light(const MeshDev& mesh, const LightDev& lights, ui
     point = p0 * b_u + p1 * b_v + p2 * (1.0f - b_u - b_v);
     normal = normalize3(cross3(p1 - p0, p2 - p0));
     pdf_area = 1.0f / lights.total_area;
-}
-
-// PowerHeuristic, src/common/cuda_utilities.h:193-197
-static __device__ float power_heuristic(float f, float g) {
-    float f2 = f * f;
-    float g2 = g * g;
-    return f2 / (f2 + g2 + 1e-5f);
 }
 
 }  // namespace ptb

@@ -3,6 +3,7 @@
 // warps pull 32-ray batches from the queue through a device-side cursor, and the queue length is
 // read on the device (no host round trip per bounce).
 #include "raycast.cuh"
+#include "logic.cuh"
 #include "render.cuh"
 
 namespace ptb {
@@ -19,27 +20,36 @@ __device__ __forceinline__ int warp_fetch(int* cursor) {
     return __shfl_sync(0xffffffffu, base, 0);
 }
 
+// FUSE_LOGIC: run the Logic stage (logic.cuh) on each path the moment its extension ray is done, while the hit
+// record is in registers -- the frame graph's form.  Without it this is the reference's TraceExtensionRay alone
+// (staged API, ptb_time_raycast).
+template <bool FUSE_LOGIC>
 __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_extension(FrameDev f, int bounce, int* cursor) {
     __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
-    const int count = f.ctr[bounce * CTR_STRIDE + CTR_EXT];
+    int* ctr = f.ctr + bounce * CTR_STRIDE;
+    const int count = ctr[CTR_EXT];
     int* my_stack = stack + threadIdx.x;
     for (int base = warp_fetch(cursor); base < count; base = warp_fetch(cursor)) {
         int i = base + (threadIdx.x & 31);
-        if (i >= count) continue;
-        int path = __ldg(&f.q_ext[i]);
-        float4 o4 = f.pool.ray_ori[path];
-        float4 d4 = f.pool.ray_dir_dist[path];
-        Hit h = trace_closest(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS);
-        // write-back, src/kernels/ray_cast.cu:111-121
-        if (h.prim == -1) {
-            f.pool.ray_dir_dist[path].w = -1.0f;
-            f.pool.hit_geom_id[path] = -1;
-        } else {
-            f.pool.ray_dir_dist[path].w = h.t;
-            f.pool.material_id[path] = h.mat;
-            f.pool.hit_geom_id[path] = h.prim;
-            f.pool.hit_uv[path] = make_float4(h.u, h.v, 0.0f, 0.0f);
+        int queue = -1, path = -1;
+        if (i < count) {
+            path = __ldg(&f.q_ext[i]);
+            float4 o4 = f.pool.ray_ori[path];
+            float4 d4 = f.pool.ray_dir_dist[path];
+            Hit h = trace_closest(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS);
+            // write-back, src/kernels/ray_cast.cu:111-121
+            if (h.prim == -1) {
+                f.pool.ray_dir_dist[path].w = -1.0f;
+                f.pool.hit_geom_id[path] = -1;
+            } else {
+                f.pool.ray_dir_dist[path].w = h.t;
+                f.pool.material_id[path] = h.mat;
+                f.pool.hit_geom_id[path] = h.prim;
+                f.pool.hit_uv[path] = make_float4(h.u, h.v, 0.0f, 0.0f);
+            }
+            if (FUSE_LOGIC) queue = logic_path<true>(f, path, h.prim, h.mat, make_float4(d4.x, d4.y, d4.z, h.t));
         }
+        if (FUSE_LOGIC) logic_dispatch(f, ctr, queue, path);
     }
 }
 
@@ -207,8 +217,9 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_
 
 static inline int rc_grid(const LaunchCfg& c) { return c.num_sms * (c.rc_blocks > 0 ? c.rc_blocks : 8); }
 
-static void run_extension(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s) {
-    if (c.rc_variant == 0) k_trace_extension<<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
+static void run_extension(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s, bool fuse_logic = false) {
+    if (fuse_logic) k_trace_extension<true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
+    else if (c.rc_variant == 0) k_trace_extension<false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
     else if (c.rc_variant == 1) k_trace_extension_pl<false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, c.rc_refill);
     else k_trace_extension_pl<true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, c.rc_refill);
 }
@@ -218,8 +229,8 @@ int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, cons
     return 1;
 }
 
-int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
-    run_extension(f, bounce, f.ctr + bounce * CTR_STRIDE + CTR_WORK_EXT, c, s);
+int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic) {
+    run_extension(f, bounce, f.ctr + bounce * CTR_STRIDE + CTR_WORK_EXT, c, s, fuse_logic);
     if (bounce == 0) return 1;   // no shadow rays exist before the first Shade (counter zeroed by RayGen, src/kernels/ray_gen.cu:121-124)
     // the DFS stack never holds more than one entry per tree level: size it from the measured LBVH depth
     const int g = rc_grid(c);

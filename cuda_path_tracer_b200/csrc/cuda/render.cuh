@@ -39,13 +39,15 @@ struct LaunchCfg {
     int rc_variant;           // RayCast scheduling: 0 = one 32-ray batch per warp fetch, 1 = persistent lanes with refill
     int rc_refill;            // variant 1: refill once this many lanes of a warp are idle
     int rc_blocks;            // resident blocks per SM the persistent grids are sized for
+    int fuse_logic;           // frame graph: Logic runs in the tail of the extension RayCast kernel
 };
 
 // Each returns the number of kernels it enqueued (for ptb_stats.kernel_launches).
 int launch_clear_accumulators(const FrameDev& f, cudaStream_t s);
 int launch_raygen(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);   // iteration is read from *f.iteration
 int launch_set_iteration(const FrameDev& f, int iteration, cudaStream_t s);
-int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);          // extension + shadow
+// extension + shadow rays; fuse_logic: the extension kernel also runs the Logic stage on each finished path
+int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic = false);
 // Extension rays only, with a caller-provided (zeroed) work cursor: used to time the kernel alone.
 int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s);
 int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);

@@ -14,6 +14,7 @@
 //   * each path owns its pixel, so the emission / environment adds never contend (they stay
 //     atomicAdd = fire-and-forget RED, and stay un-fused with the product that feeds them).
 #include "bsdf.cuh"
+#include "logic.cuh"
 #include "render.cuh"
 
 namespace ptb {
@@ -29,13 +30,35 @@ __global__ void k_clear(float* a, float* b, size_t n) {
     for (; i < n; i += stride) { a[i] = 0.0f; b[i] = 0.0f; }
 }
 
+// Queue position -> path slot.  The reference fills its first queue in pixel order (queue[i] = i,
+// src/kernels/ray_gen.cu:76), so a warp of RayCast gets a 32x1 run of pixels.  Queue ORDER is unobservable
+// (every per-path result is independent of its position), so the first queue is laid out in 8x4 pixel tiles
+// instead: a warp's rays span a quarter of the width, stay on nearby surfaces for the following bounces, and
+// touch fewer distinct BVH records per load -- which is what bounds RayCast (L1 wavefronts).
+// Pixels outside the largest (8k x 4m) region keep their linear order.
+__device__ __forceinline__ int tiled_slot(int i, int width, int rows) {
+    const int w8 = width & ~7, h4 = rows & ~3;
+    const int tiled = w8 * h4;
+    if (i >= tiled) {
+        int j = i - tiled;                                   // right strip (rows < h4), then the bottom rows
+        int strip = (width - w8) * h4;
+        if (j < strip) { int sw = width - w8; return (j / sw) * width + w8 + (j % sw); }
+        return h4 * width + (j - strip);
+    }
+    int tile = i >> 5, lane = i & 31;
+    int tiles_per_row = w8 >> 3;
+    int ty = tile / tiles_per_row, tx = tile - ty * tiles_per_row;
+    return (ty * 4 + (lane >> 3)) * width + tx * 8 + (lane & 7);
+}
+
 __global__ void __launch_bounds__(kThreads) k_raygen(FrameDev f) {
     const int iter = *f.iteration;
-    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const int qpos = blockIdx.x * blockDim.x + threadIdx.x;
     // counter rows: everything zero except the first extension queue, which holds every path
     int nctr = (f.trace_depth + 1) * CTR_STRIDE;
-    if (slot < nctr) f.ctr[slot] = (slot == CTR_EXT) ? f.num_paths : 0;
-    if (slot >= f.num_paths) return;
+    if (qpos < nctr) f.ctr[qpos] = (qpos == CTR_EXT) ? f.num_paths : 0;
+    if (qpos >= f.num_paths) return;
+    const int slot = tiled_slot(qpos, f.tile.width, f.num_paths / f.tile.width);
     int pixel_idx = f.tile.global_pixel(slot);
     int x = pixel_idx % f.cam.res_x;
     int y = pixel_idx / f.cam.res_x;
@@ -57,44 +80,12 @@ __global__ void __launch_bounds__(kThreads) k_raygen(FrameDev f) {
     f.pool.throughput_pdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
     f.pool.remaining_bounces[slot] = f.trace_depth;
     f.pool.rng_state[slot] = seed;
-    f.q_ext[slot] = slot;
-}
-
-// ---- surface interpolation (GetSurfaceProperties, src/common/cuda_utilities.h:279-326) ---------
-__device__ __forceinline__ void surface_properties(const FrameDev& f, int prim, float u, float v, const Mat& mat, Vec3& N, float& uvx, float& uvy) {
-    int4 im = __ldg(&f.mesh.indices_matid[prim]);
-    float w = 1.0f - u - v;
-    float2 uv0 = __ldg(&f.mesh.uv[im.x]), uv1 = __ldg(&f.mesh.uv[im.y]), uv2 = __ldg(&f.mesh.uv[im.z]);
-    uvx = w * uv0.x + u * uv1.x + v * uv2.x;
-    uvy = w * uv0.y + u * uv1.y + v * uv2.y;
-    Vec3 n0 = make_v3(__ldg(&f.mesh.nor[im.x])), n1 = make_v3(__ldg(&f.mesh.nor[im.y])), n2 = make_v3(__ldg(&f.mesh.nor[im.z]));
-    Vec3 Ns = normalize3(w * n0 + u * n1 + v * n2);
-    if (mat.normal_tex < 0) { N = Ns; return; }
-    Vec3 t0 = make_v3(__ldg(&f.mesh.tangent[im.x])), t1 = make_v3(__ldg(&f.mesh.tangent[im.y])), t2 = make_v3(__ldg(&f.mesh.tangent[im.z]));
-    Vec3 Ti = w * t0 + u * t1 + v * t2;
-    Vec3 B = normalize3(cross3(Ns, Ti));
-    Vec3 T = cross3(B, Ns);
-    float4 s = tex2D<float4>(__ldg(&f.tex.handles[mat.normal_tex]), uvx, uvy);
-    Vec3 m(s.x * 2.0f - 1.0f, s.y * 2.0f - 1.0f, s.z * 2.0f - 1.0f);
-    // glm::mat3(T, B, N) * m = T*m.x + B*m.y + N*m.z (type_mat3x3.inl:487-493)
-    N = normalize3(Vec3(T.x * m.x + B.x * m.y + Ns.x * m.z, T.y * m.x + B.y * m.y + Ns.y * m.z, T.z * m.x + B.z * m.y + Ns.z * m.z));
+    f.q_ext[qpos] = slot;
 }
 
 __device__ __forceinline__ Vec3 pow3(Vec3 c, float e) { return Vec3(powf(c.x, e), powf(c.y, e), powf(c.z, e)); }
 
-// warp-aggregated append at a converged point: returns the slot for lanes with `want`
-__device__ __forceinline__ int warp_append(bool want, int* counter) {
-    unsigned int mask = __ballot_sync(0xffffffffu, want);
-    if (mask == 0) return -1;
-    int lane = threadIdx.x & 31;
-    int leader = __ffs(mask) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(counter, __popc(mask));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    return want ? base + __popc(mask & ((1u << lane) - 1u)) : -1;
-}
-
-// ---- Logic (PathLogicKernel, src/kernels/logic.cu:31-192) --------------------------------------
+// ---- Logic (PathLogicKernel, src/kernels/logic.cu:31-192) as its own kernel: the staged API --------------
 __global__ void __launch_bounds__(kThreads) k_logic(FrameDev f, int bounce) {
     int* ctr = f.ctr + bounce * CTR_STRIDE;
     const int count = ctr[CTR_EXT];
@@ -106,70 +97,9 @@ __global__ void __launch_bounds__(kThreads) k_logic(FrameDev f, int bounce) {
         int idx = -1;
         if (i < count) {
             idx = __ldg(&f.q_ext[i]);
-            int hit = f.pool.hit_geom_id[idx];
-            int remaining = f.pool.remaining_bounces[idx];
-            float4 tp = f.pool.throughput_pdf[idx];
-            Vec3 throughput(tp.x, tp.y, tp.z);
-            float last_pdf = tp.w;
-            bool first = (remaining == f.trace_depth);
-            float* pix = f.indirect + 3 * (size_t)idx;
-            if (hit == -1) {
-                if (f.tex.env_tex_id >= 0) {
-                    float4 dd = f.pool.ray_dir_dist[idx];
-                    Vec3 dir = normalize3(Vec3(dd.x, dd.y, dd.z));
-                    float phi = atan2f(dir.z, dir.x);
-                    if (phi < 0) phi += PTB_TWO_PI;
-                    float theta = acosf(clampf(dir.y, -1.0f, 1.0f));
-                    float eu = phi * PTB_INV_TWO_PI;
-                    float ev = theta * PTB_INV_PI;
-                    float4 e4 = tex2D<float4>(__ldg(&f.tex.handles[f.tex.env_tex_id]), eu, ev);
-                    Vec3 env(e4.x, e4.y, e4.z);
-                    float mis = 1.0f;
-                    if (!first) {
-                        float pdf_bsdf = last_pdf;
-                        float pdf_env = tex2D<float>(__ldg(&f.tex.handles[f.tex.pdf_map_id]), eu, ev);
-                        if (pdf_bsdf > 1e10f) mis = 1.0f;
-                        else mis = (pdf_bsdf * pdf_bsdf) / (pdf_bsdf * pdf_bsdf + pdf_env * pdf_env + PTB_EPSILON);
-                    }
-                    Vec3 add = throughput * env * mis;
-                    atomicAdd(pix + 0, add.x); atomicAdd(pix + 1, add.y); atomicAdd(pix + 2, add.z);   // a separate add: `pix += a*b` would fuse
-                }
-                f.pool.remaining_bounces[idx] = -1;
-            } else {
-                int mat_id = f.pool.material_id[idx];
-                Mat m = load_material(f.materials, mat_id);
-                if (m.emittance > 0.0f) {
-                    float4 huv = f.pool.hit_uv[idx];
-                    Vec3 N; float uvx, uvy;
-                    surface_properties(f, hit, huv.x, huv.y, m, N, uvx, uvy);
-                    float4 dd = f.pool.ray_dir_dist[idx];
-                    Vec3 wo = -Vec3(dd.x, dd.y, dd.z);
-                    float mis = 1.0f;
-                    if (!first && f.lights.num_lights > 0) {
-                        bool prev_specular = (last_pdf > (PTB_PDF_DIRAC_DELTA * 0.9f));
-                        if (!prev_specular) {
-                            float dist = dd.w;
-                            float cos_light = fmaxf(dot3(N, wo), 0.0f);
-                            if (cos_light > PTB_EPSILON) {
-                                float pdf_area = 1.0f / f.lights.total_area;
-                                float pdf_sa = pdf_area * (dist * dist) / cos_light;
-                                mis = power_heuristic(last_pdf, pdf_sa);
-                            } else mis = 0.0f;
-                        }
-                    }
-                    Vec3 add = throughput * m.basecolor * m.emittance * mis;
-                    atomicAdd(pix + 0, add.x); atomicAdd(pix + 1, add.y); atomicAdd(pix + 2, add.z);   // a separate add: `pix += a*b` would fuse
-                    f.pool.remaining_bounces[idx] = -1;
-                } else {
-                    queue = m.type;
-                }
-            }
+            queue = logic_path<false>(f, idx, f.pool.hit_geom_id[idx], 0, make_float4(0.0f, 0.0f, 0.0f, 0.0f));
         }
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
-            int pos = warp_append(queue == q, &ctr[CTR_PBR + q]);
-            if (pos >= 0) f.q_mat[q][pos] = idx;
-        }
+        logic_dispatch(f, ctr, queue, idx);
     }
 }
 

@@ -35,6 +35,7 @@ struct ptb_renderer {
     LbvhBuffers lbvh;
     FrameDev frame{};
     LaunchCfg launch{};
+    float last_batch_ms = 0.0f;
     size_t device_bytes = 0;
 
     // frame graph
@@ -133,8 +134,10 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
     int n = 0;
     n += launch_raygen(f, r->launch, s);
     for (int b = 0; b < f.trace_depth; b++) {
-        n += launch_trace(f, b, r->launch, s);
-        n += launch_logic(f, b, r->launch, s);
+        // whole frames run Logic inside the extension RayCast kernel; the staged API keeps the stages apart
+        const bool fuse = r->launch.fuse_logic != 0;
+        n += launch_trace(f, b, r->launch, s, fuse);
+        if (!fuse) n += launch_logic(f, b, r->launch, s);
         // Rays produced by the last Shade are never traced (loop bound src/pathtrace_wavefront.cu:281,
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
         if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
@@ -220,6 +223,7 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         r->launch.rc_variant = knob("PTB_RC_VARIANT", 0);
         r->launch.rc_refill = knob("PTB_RC_REFILL", 8);
         r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
+        r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);
     }
 
     FrameDev& f = r->frame;
@@ -533,6 +537,21 @@ int ptb_build_lbvh(int32_t device, const float* pos4, int32_t V, const int32_t* 
 }
 
 // ===================================================================== batched RayCast ==========
+namespace {
+struct BatchTimer {            // device time of one batched RayCast kernel -> ptb_stats.last_batch_ms
+    ptb_renderer* r; cudaEvent_t e0 = nullptr, e1 = nullptr;
+    explicit BatchTimer(ptb_renderer* r_) : r(r_) {
+        if (cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess) cudaEventRecord(e0, r->stream);
+    }
+    void stop() { if (e1) cudaEventRecord(e1, r->stream); }
+    ~BatchTimer() {
+        if (e0 && e1 && cudaEventSynchronize(e1) == cudaSuccess) cudaEventElapsedTime(&r->last_batch_ms, e0, e1);
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+    }
+};
+}  // namespace
+
 int ptb_trace_closest(ptb_renderer* r, const float* ori4, const float* dir4, int32_t n, int32_t* hit, float* t, float* u, float* v) {
     if (!r || !ori4 || !dir4 || !hit || !t || !u || !v) return fail(PTB_ERR_INVALID, "ptb_trace_closest: null argument");
     if (n < 0) return fail(PTB_ERR_INVALID, "ptb_trace_closest: negative count");
@@ -546,7 +565,9 @@ int ptb_trace_closest(ptb_renderer* r, const float* ori4, const float* dir4, int
     int* dhit = (int*)(base + 32 * N); float* dt = (float*)(base + 36 * N); float* du = (float*)(base + 40 * N); float* dv = (float*)(base + 44 * N);
     CU(cudaMemcpyAsync(dori, ori4, 16 * N, cudaMemcpyHostToDevice, r->stream));
     CU(cudaMemcpyAsync(ddir, dir4, 16 * N, cudaMemcpyHostToDevice, r->stream));
+    BatchTimer timer(r);
     r->kernel_launches += launch_trace_batch_closest(r->frame.bvh, dori, ddir, n, dhit, dt, du, dv, r->cursors + kMaxTimed, r->launch, r->stream);
+    timer.stop();
     CU(cudaMemcpyAsync(hit, dhit, 4 * N, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaMemcpyAsync(t, dt, 4 * N, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaMemcpyAsync(u, du, 4 * N, cudaMemcpyDeviceToHost, r->stream));
@@ -567,7 +588,9 @@ int ptb_trace_occluded(ptb_renderer* r, const float* ori_tmax4, const float* dir
     float4* dori = (float4*)base; float4* ddir = (float4*)(base + 16 * N); int* docc = (int*)(base + 32 * N);
     CU(cudaMemcpyAsync(dori, ori_tmax4, 16 * N, cudaMemcpyHostToDevice, r->stream));
     CU(cudaMemcpyAsync(ddir, dir4, 16 * N, cudaMemcpyHostToDevice, r->stream));
+    BatchTimer timer(r);
     r->kernel_launches += launch_trace_batch_occluded(r->frame.bvh, dori, ddir, n, docc, r->cursors + kMaxTimed, r->frame.error_flag, r->launch, r->stream);
+    timer.stop();
     CU(cudaMemcpyAsync(occluded, docc, 4 * N, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaStreamSynchronize(r->stream));
     return check_device_error(r);
@@ -716,6 +739,7 @@ int ptb_get_stats(ptb_renderer* r, ptb_stats* out) {
     out->lbvh_build_ms = r->lbvh_build_ms;
     out->lbvh_max_depth = r->lbvh_max_depth;
     out->num_triangles = r->lbvh.num_triangles;
+    out->last_batch_ms = r->last_batch_ms;
     return check_device_error(r);
 }
 

@@ -267,7 +267,7 @@ typedef struct ptb_stats {
     float lbvh_build_ms;       /* "LBVH Build Time" (src/bvh.cu:467-498) */
     int32_t lbvh_max_depth;    /* "LBVH Max Tree Depth" (src/bvh.cu:416-454) */
     int32_t num_triangles;
-    int32_t reserved;
+    float last_batch_ms;       /* device time of the kernel of the most recent ptb_trace_closest / ptb_trace_occluded (CUDA events) */
 } ptb_stats;
 int ptb_get_stats(ptb_renderer* r, ptb_stats* out);
 int ptb_stats_reset(ptb_renderer* r);
