@@ -229,16 +229,24 @@ int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, cons
     return 1;
 }
 
-int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic) {
+int launch_trace_extension(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic) {
     run_extension(f, bounce, f.ctr + bounce * CTR_STRIDE + CTR_WORK_EXT, c, s, fuse_logic);
-    if (bounce == 0) return 1;   // no shadow rays exist before the first Shade (counter zeroed by RayGen, src/kernels/ray_gen.cu:121-124)
+    return 1;
+}
+
+int launch_trace_shadow(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
+    if (bounce == 0) return 0;   // no shadow rays exist before the first Shade (counter zeroed by RayGen, src/kernels/ray_gen.cu:121-124)
     // the DFS stack never holds more than one entry per tree level: size it from the measured LBVH depth
     const int g = rc_grid(c);
     if (c.shadow_deep == 3) k_trace_shadow<256, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
     else if (c.shadow_deep == 0) k_trace_shadow<32, true><<<c.num_sms * PTB_SH_MINBLOCKS, PTB_RC_THREADS, 0, s>>>(f, bounce);
     else if (c.shadow_deep == 1) k_trace_shadow<48, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
     else k_trace_shadow<64, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
-    return 2;
+    return 1;
+}
+
+int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic) {
+    return launch_trace_extension(f, bounce, c, s, fuse_logic) + launch_trace_shadow(f, bounce, c, s);
 }
 
 // ---- batched entry points (ptb_trace_closest / ptb_trace_occluded) ---------------------------

@@ -40,6 +40,7 @@ struct LaunchCfg {
     int rc_refill;            // variant 1: refill once this many lanes of a warp are idle
     int rc_blocks;            // resident blocks per SM the persistent grids are sized for
     int fuse_logic;           // frame graph: Logic runs in the tail of the extension RayCast kernel
+    int overlap_shadow;       // frame graph: TraceShadow(b) runs beside TraceExtension(b) on a forked branch
 };
 
 // Each returns the number of kernels it enqueued (for ptb_stats.kernel_launches).
@@ -48,6 +49,8 @@ int launch_raygen(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);   // i
 int launch_set_iteration(const FrameDev& f, int iteration, cudaStream_t s);
 // extension + shadow rays; fuse_logic: the extension kernel also runs the Logic stage on each finished path
 int launch_trace(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic = false);
+int launch_trace_extension(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s, bool fuse_logic);
+int launch_trace_shadow(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);   // 0 launches at bounce 0
 // Extension rays only, with a caller-provided (zeroed) work cursor: used to time the kernel alone.
 int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s);
 int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);

@@ -209,31 +209,24 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
     f.pool.rng_state[idx] = seed;
 }
 
-__global__ void __launch_bounds__(kThreads) k_shade(FrameDev f, int bounce) {
+// One kernel per material queue: a queue's launch carries only its own model's registers and local frame (the
+// four models in one kernel cost 95 registers and an 864-byte frame per thread, most of it dead for any given warp).
+template <int TYPE>
+__global__ void __launch_bounds__(kThreads) k_shade(const __grid_constant__ FrameDev f, int bounce) {
     const int* ctr = f.ctr + bounce * CTR_STRIDE;
     int* next = f.ctr + (bounce + 1) * CTR_STRIDE;
-    // chunk table: queue q owns chunks [c0[q], c0[q+1]) of 32 paths each
-    int n[4], c0[5];
-    c0[0] = 0;
-#pragma unroll
-    for (int q = 0; q < 4; q++) { n[q] = ctr[CTR_PBR + q]; c0[q + 1] = c0[q] + ((n[q] + 31) >> 5); }
-    const int lane = threadIdx.x & 31;
-    const int warps_total = (gridDim.x * blockDim.x) >> 5;
-    const int warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    for (int chunk = warp_id; chunk < c0[4]; chunk += warps_total) {
-        int q = (chunk >= c0[3]) ? 3 : (chunk >= c0[2]) ? 2 : (chunk >= c0[1]) ? 1 : 0;
-        int i = ((chunk - c0[q]) << 5) + lane;
-        bool active = i < n[q];
+    const int n = ctr[CTR_PBR + TYPE];
+    const int stride = gridDim.x * blockDim.x;
+    const int rounds = (n + stride - 1) / stride;
+    for (int r = 0; r < rounds; r++) {
+        int i = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
         ShadeOut out;
         out.push_ext = false;
         out.push_shadow = false;
         int idx = -1;
-        if (active) {
-            idx = __ldg(&f.q_mat[q][i]);
-            if (q == MAT_PBR) shade_path<MAT_PBR>(f, idx, out);
-            else if (q == MAT_DIFFUSE) shade_path<MAT_DIFFUSE>(f, idx, out);
-            else if (q == MAT_REFLECT) shade_path<MAT_REFLECT>(f, idx, out);
-            else shade_path<MAT_REFRACT>(f, idx, out);
+        if (i < n) {
+            idx = __ldg(&f.q_mat[TYPE][i]);
+            shade_path<TYPE>(f, idx, out);
         }
         int sp = warp_append(out.push_shadow, &next[CTR_SHADOW]);
         if (sp >= 0) {
@@ -311,8 +304,11 @@ int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t
     return 1;
 }
 int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
-    k_shade<<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
-    return 1;
+    k_shade<MAT_PBR><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    k_shade<MAT_DIFFUSE><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    k_shade<MAT_REFLECT><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    k_shade<MAT_REFRACT><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    return 4;
 }
 int launch_frame_end(const FrameDev& f, const LaunchCfg&, cudaStream_t s) {
     k_frame_end<<<1, 32, 0, s>>>(f);

@@ -26,6 +26,8 @@ struct ptb_renderer {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t side = nullptr;          // forked branch of the frame (shadow rays beside extension rays)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     ptb_config cfg{};
 
     // scene replica on the device
@@ -136,8 +138,21 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
     for (int b = 0; b < f.trace_depth; b++) {
         // whole frames run Logic inside the extension RayCast kernel; the staged API keeps the stages apart
         const bool fuse = r->launch.fuse_logic != 0;
-        n += launch_trace(f, b, r->launch, s, fuse);
-        if (!fuse) n += launch_logic(f, b, r->launch, s);
+        if (b > 0 && r->launch.overlap_shadow && r->side) {
+            // TraceShadow(b) reads what Shade(b-1) queued and only adds to `direct`; TraceExtension(b) + Logic(b) touch
+            // the path pool and `indirect`: independent until Shade(b), so they run as two branches of the graph and
+            // each fills the other's tail.
+            cudaEventRecord(r->ev_fork, s);
+            cudaStreamWaitEvent(r->side, r->ev_fork, 0);
+            n += launch_trace_shadow(f, b, r->launch, r->side);
+            n += launch_trace_extension(f, b, r->launch, s, fuse);
+            if (!fuse) n += launch_logic(f, b, r->launch, s);
+            cudaEventRecord(r->ev_join, r->side);
+            cudaStreamWaitEvent(s, r->ev_join, 0);
+        } else {
+            n += launch_trace(f, b, r->launch, s, fuse);
+            if (!fuse) n += launch_logic(f, b, r->launch, s);
+        }
         // Rays produced by the last Shade are never traced (loop bound src/pathtrace_wavefront.cu:281,
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
         if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
@@ -186,6 +201,9 @@ int ptb_free(ptb_renderer* r) {
     if (r->scratch) cudaFree(r->scratch);
     lbvh_free(r->lbvh);
     if (r->own_stream && r->stream) cudaStreamDestroy(r->stream);
+    if (r->side) cudaStreamDestroy(r->side);
+    if (r->ev_fork) cudaEventDestroy(r->ev_fork);
+    if (r->ev_join) cudaEventDestroy(r->ev_join);
     delete r;
     return PTB_OK;
 }
@@ -224,6 +242,12 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         r->launch.rc_refill = knob("PTB_RC_REFILL", 8);
         r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
         r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);
+        r->launch.overlap_shadow = knob("PTB_OVERLAP_SHADOW", 1);
+        if (r->launch.overlap_shadow) {
+            TRYCU(cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking));
+            TRYCU(cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming));
+            TRYCU(cudaEventCreateWithFlags(&r->ev_join, cudaEventDisableTiming));
+        }
     }
 
     FrameDev& f = r->frame;
