@@ -138,7 +138,10 @@ static __device__ float pdf_pbr(V3R wo, V3R wi, V3R N, const Mat& m) {
 static __device__ Vec3 eval_diffuse(const Mat& m, V3R N, V3R wi) { return m.basecolor * PTB_INV_PI; }
 
 // evalBSDF / pdfBSDF for the two materials that do NEE (src/interactions.cu:191-216)
-PTB_BSDF_ENTRY Vec3 eval_bsdf(Vec3 wo, Vec3 wi, Vec3 N, Mat m) {
+// (The reference passes these four by value; a by-value glm::vec3 / Material is a hidden reference to a caller-side
+// copy, so the callee's loads and arithmetic are the same -- checked with tools/ptx_alpha.py -- and the caller saves
+// 80 bytes of local-memory copies per call.)
+PTB_BSDF_ENTRY Vec3 eval_bsdf(const Vec3& wo, const Vec3& wi, const Vec3& N, const Mat& m) {
     if (m.type == MAT_PBR) return eval_pbr(wo, wi, N, m);
     else if (m.type == MAT_DIFFUSE) return eval_diffuse(m, N, wi);
     else return Vec3(0.0f);
@@ -148,7 +151,7 @@ static __device__ float pdf_diffuse(V3R wi, V3R N) {
     if (NdotL <= 0.0f) return 0.0f;
     return NdotL * PTB_INV_PI;
 }
-PTB_BSDF_ENTRY float pdf_bsdf(Vec3 wo, Vec3 wi, Vec3 N, Mat m) {
+PTB_BSDF_ENTRY float pdf_bsdf(const Vec3& wo, const Vec3& wi, const Vec3& N, const Mat& m) {
     if (m.type == MAT_PBR) return pdf_pbr(wo, wi, N, m);
     else if (m.type == MAT_DIFFUSE) return pdf_diffuse(wi, N);
     else if (m.type == MAT_REFLECT) return PTB_PDF_DIRAC_DELTA;

@@ -211,8 +211,11 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
 
 // One kernel per material queue: a queue's launch carries only its own model's registers and local frame (the
 // four models in one kernel cost 95 registers and an 864-byte frame per thread, most of it dead for any given warp).
+#ifndef PTB_SHADE_MINBLOCKS
+#define PTB_SHADE_MINBLOCKS 1
+#endif
 template <int TYPE>
-__global__ void __launch_bounds__(kThreads) k_shade(const __grid_constant__ FrameDev f, int bounce) {
+__global__ void __launch_bounds__(kThreads, PTB_SHADE_MINBLOCKS) k_shade(const __grid_constant__ FrameDev f, int bounce) {
     const int* ctr = f.ctr + bounce * CTR_STRIDE;
     int* next = f.ctr + (bounce + 1) * CTR_STRIDE;
     const int n = ctr[CTR_PBR + TYPE];
