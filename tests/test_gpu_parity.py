@@ -252,3 +252,34 @@ def test_sample_index_partition_matches_single_renderer(fire_small):
     b.render(1); b.clear(); b.render(3)
     assert _bits(a.resolve(1, capi.IMG_SUM_RGB32F), b.resolve(1, capi.IMG_SUM_RGB32F))
     one.free(); a.free(); b.free()
+
+
+def test_stress_10m_lbvh_and_raycast_vs_oracle():
+    """BASELINE config[3]: 10,000,000 procedural triangles injected as arrays.  LBVH bit-exact against the C oracle,
+    closest / any hit bit-exact on a ray sample, hierarchy invariants of the reference's TestHierarchyLogic."""
+    pos, nor, idx, mat = scenegen.heightfield_arrays(10_000_000)
+    s = ptb.Scene.from_arrays(pos, nor, idx, mat, scenegen.stress_materials(), scenegen.stress_camera((640, 360)))
+    r = ptb.Renderer(s)
+    pos4, im = s.array("pos"), s.array("indices_matid")
+    ref = orc.build_lbvh(pos4, im)
+    for name in ("aabb_min", "aabb_max", "primitive_indices", "morton_codes", "child_nodes", "parent", "escape_indices", "world_aabb"):
+        assert _bits(r.lbvh(name), ref[name]), name
+    assert orc.check_hierarchy(ref["child_nodes"], ref["parent"]) == 0
+    st = r.stats()
+    assert st.num_triangles == 10_000_000 and 0 < st.lbvh_build_ms < 100 and st.lbvh_max_depth <= 64
+    # the rays of a real first bounce
+    r.stage(capi.STAGE_RAYGEN, 1)
+    r.stage(capi.STAGE_TRACE); r.stage(capi.STAGE_LOGIC); r.stage(capi.STAGE_SHADE)
+    q = r.queue("extension")[:60000]
+    ori, d = r.path_field("ray_ori")[q].copy(), r.path_field("ray_dir_dist")[q].copy()
+    hit, t, u, v = r.trace_closest(ori, d)
+    h2, t2, u2, v2 = orc.trace_closest(ref, pos4, im, ori, d, threads=8)
+    assert np.array_equal(hit, h2)
+    m = hit >= 0
+    assert _bits(t, t2) and _bits(u[m], u2[m]) and _bits(v[m], v2[m])
+    ori[:, 3] = 25.0
+    assert np.array_equal(r.trace_occluded(ori, d), orc.trace_occluded(ref, pos4, im, ori, d, threads=8))
+    r.render(1, 2)
+    a = r.resolve(2)
+    assert np.isfinite(a).all() and a.max() > 0
+    r.free()
