@@ -20,6 +20,8 @@ class PtbError(RuntimeError):
 
 OK, ERR_INVALID, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_STATE = 0, -1, -2, -3, -4, -5, -6
 IMG_SUM_RGB32F, IMG_MEAN_RGB32F, IMG_RGBA8 = 0, 1, 2
+IMG_VIEW_NORMALS, IMG_VIEW_DEPTH, IMG_VIEW_ALBEDO, IMG_VIEW_MOTION, IMG_STEPS_I32 = 3, 4, 5, 6, 7
+GB_DEPTH, GB_NORMAL_MATID, GB_ALBEDO, GB_MOTION = 0, 1, 2, 3
 STAGE_RAYGEN, STAGE_TRACE, STAGE_LOGIC, STAGE_SHADE = 0, 1, 2, 3
 Q_EXTENSION, Q_SHADOW, Q_PBR, Q_DIFFUSE, Q_REFLECTION, Q_REFRACTION = range(6)
 
@@ -51,7 +53,7 @@ class SceneInfo(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("trace_depth", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("reserved", C.c_int32 * 8)]
+                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("reserved", C.c_int32 * 7)]
 
 
 class TileInfo(C.Structure):
@@ -84,6 +86,8 @@ SIGNATURES = {
     "ptb_render": (C.c_int, [P, C.c_int32]),
     "ptb_render_many": (C.c_int, [P, C.c_int32, C.c_int32]),
     "ptb_clear_accumulators": (C.c_int, [P]),
+    "ptb_get_gbuffer": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
+    "ptb_visualize_lbvh": (C.c_int, [P, P, C.c_int32, C.c_int32]),
     "ptb_sync": (C.c_int, [P]),
     "ptb_set_stream": (C.c_int, [P, P]),
     "ptb_resolve": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32]),

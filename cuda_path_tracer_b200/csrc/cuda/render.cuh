@@ -11,6 +11,15 @@ namespace ptb {
 // (the reference does 6 blocking D2H reads + 6 memsets per bounce, src/pathtrace_wavefront.cu:286-343).
 enum { CTR_WORK_EXT = 6, CTR_WORK_SHADOW = 7 };   // work-fetch cursors of the persistent RayCast kernels
 
+struct Mat4 { float m[4][4]; };          // glm::mat4: m[column][row]
+
+struct GBufferDev {                      // first-bounce G-buffer, one entry per owned pixel (src/wavefront_internal.cu:286-300)
+    float* depth;                        // hit distance, -1000 for the sky
+    float4* normal_matid;                // geometric normal, (float)material id (-1 sky)
+    float4* albedo;                      // base colour x texture^2.2, w = 1 (sky: 1,1,1,0)
+    float2* motion;                      // screen-space motion in pixels: uv(current view-proj) - uv(previous)
+};
+
 struct FrameDev {
     PathPool pool;
     ShadowQueueDev shadow;
@@ -20,6 +29,7 @@ struct FrameDev {
     unsigned long long* ray_totals;   // [2] extension / shadow rays since the last stats reset
     int* iteration;           // 1-based sample index of the frame being rendered; advanced by frame_end
     int* error_flag;          // set by a kernel on traversal-stack overflow
+    Mat4* view_proj;          // [2] current / previous view-projection (G-buffer motion vectors); null when the G-buffer is off
     float* direct;            // 3 floats per owned pixel (d_direct_image, src/wavefront_internal.h:26)
     float* indirect;          // (d_indirect_image, :27)
     MeshDev mesh;
@@ -57,6 +67,10 @@ int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t
 int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
 int launch_frame_end(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);                   // ray statistics
 int launch_resolve(const FrameDev& f, void* dst, int format, int iteration, cudaStream_t s);
+// headless views (views.cu)
+int launch_gbuffer(const FrameDev& f, const GBufferDev& g, cudaStream_t s);
+int launch_view(const GBufferDev& g, int n, void* dst_rgba8, int mode, cudaStream_t s);   // SendImageToPBOKernel modes 1-4
+int launch_bvh_heatmap(const FrameDev& f, float* out_rgb, int* out_steps, cudaStream_t s);
 
 // Batched RayCast on caller rays (ptb_trace_closest / ptb_trace_occluded): device arrays.
 int launch_trace_batch_closest(const BvhDev& bvh, const float4* ori, const float4* dir, int n, int* hit, float* t, float* u,

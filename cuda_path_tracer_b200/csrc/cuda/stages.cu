@@ -254,6 +254,7 @@ __global__ void k_frame_end(FrameDev f) {
         f.ray_totals[0] += e;
         f.ray_totals[1] += s;
         *f.iteration += 1;
+        if (f.view_proj) f.view_proj[1] = f.view_proj[0];   // prev_view_proj_mat = view_proj_mat, src/pathtrace_wavefront.cu:368
     }
 }
 

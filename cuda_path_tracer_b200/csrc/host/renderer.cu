@@ -2,6 +2,7 @@
 // per-frame CUDA graph, staged (parity) execution, read-backs.
 // Replaces pathtrace_wavefront::{PathtraceInit, Pathtrace, PathtraceFree} (reference
 // src/pathtrace_wavefront.cu:144-413) and WavefrontPathTracerState (src/wavefront_internal.cu).
+#include <cmath>
 #include <cstdlib>
 #include <cuda_runtime.h>
 
@@ -38,6 +39,8 @@ struct ptb_renderer {
     FrameDev frame{};
     LaunchCfg launch{};
     float last_batch_ms = 0.0f;
+    bool gbuffer = false;                 // ptb_config.gbuffer: first-bounce G-buffer kept every frame
+    GBufferDev gb{};
     size_t device_bytes = 0;
 
     // frame graph
@@ -131,6 +134,37 @@ static int owned_rows(const ptb_config& c, int height) {
     return rows;
 }
 
+// glm::lookAt / glm::perspective / mat4 * mat4 with GLM 0.9.6.3's operation order (gtc/matrix_transform.inl:212-231,
+// 387-412; detail/type_mat4x4.inl:686-704), as the reference evaluates them on the host every frame
+// (src/kernels/ray_gen.cu:92-103): view-projection of the scene camera for the G-buffer's motion vectors.
+static Mat4 camera_view_proj(const ptb_camera& c) {
+    using namespace ptb;
+    V3 eye(c.position[0], c.position[1], c.position[2]), center(c.look_at[0], c.look_at[1], c.look_at[2]), up(c.up[0], c.up[1], c.up[2]);
+    V3 f = normalize(center - eye);
+    V3 s = normalize(cross(f, up));
+    V3 u = cross(s, f);
+    float view[4][4] = {{1, 0, 0, 0}, {0, 1, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}};
+    view[0][0] = s.x; view[1][0] = s.y; view[2][0] = s.z;
+    view[0][1] = u.x; view[1][1] = u.y; view[2][1] = u.z;
+    view[0][2] = -f.x; view[1][2] = -f.y; view[2][2] = -f.z;
+    view[3][0] = -dot(s, eye); view[3][1] = -dot(u, eye); view[3][2] = dot(f, eye);
+    const float fovy = c.fov[1] * 0.01745329251994329576923690768489f;      // glm::radians
+    const float aspect = float(c.resolution[0]) / float(c.resolution[1]);
+    const float z_near = 0.1f, z_far = 1000.0f;
+    const float tan_half = std::tan(fovy / 2.0f);
+    float proj[4][4] = {};
+    proj[0][0] = 1.0f / (aspect * tan_half);
+    proj[1][1] = 1.0f / tan_half;
+    proj[2][2] = -(z_far + z_near) / (z_far - z_near);
+    proj[2][3] = -1.0f;
+    proj[3][2] = -(2.0f * z_far * z_near) / (z_far - z_near);
+    Mat4 vp;
+    for (int j = 0; j < 4; j++)
+        for (int i = 0; i < 4; i++)
+            vp.m[j][i] = ((proj[0][i] * view[j][0] + proj[1][i] * view[j][1]) + proj[2][i] * view[j][2]) + proj[3][i] * view[j][3];
+    return vp;
+}
+
 static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
     const FrameDev& f = r->frame;
     int n = 0;
@@ -153,6 +187,7 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
             n += launch_trace(f, b, r->launch, s, fuse);
             if (!fuse) n += launch_logic(f, b, r->launch, s);
         }
+        if (b == 0 && r->gbuffer) n += launch_gbuffer(f, r->gb, s);   // the reference's Logic writes it on the first bounce
         // Rays produced by the last Shade are never traced (loop bound src/pathtrace_wavefront.cu:281,
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
         if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
@@ -352,6 +387,27 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     TRYCU(cudaMemsetAsync(f.pool.remaining_bounces, 0xff, P * sizeof(int), r->stream));
     TRYCU(cudaMemsetAsync(f.pool.hit_geom_id, 0xff, P * sizeof(int), r->stream));
 
+    // ---- first-bounce G-buffer (initSVGF buffers, src/wavefront_internal.cu:286-300), on request
+    f.view_proj = nullptr;
+    if (cfg.gbuffer) {
+        r->gbuffer = true;
+        TRY(dev_alloc(r, r->gb.depth, P));
+        TRY(dev_alloc(r, r->gb.normal_matid, P));
+        TRY(dev_alloc(r, r->gb.albedo, P));
+        TRY(dev_alloc(r, r->gb.motion, P));
+        TRYCU(cudaMemsetAsync(r->gb.depth, 0, P * sizeof(float), r->stream));
+        TRYCU(cudaMemsetAsync(r->gb.normal_matid, 0, P * sizeof(float4), r->stream));
+        TRYCU(cudaMemsetAsync(r->gb.albedo, 0, P * sizeof(float4), r->stream));
+        TRYCU(cudaMemsetAsync(r->gb.motion, 0, P * sizeof(float2), r->stream));
+        Mat4 vp[2];
+        vp[0] = camera_view_proj(scene->camera);
+        memset(&vp[1], 0, sizeof(Mat4));                       // prev_view_proj_mat starts as glm::mat4() = identity
+        for (int i = 0; i < 4; i++) vp[1].m[i][i] = 1.0f;
+        TRY(dev_alloc(r, f.view_proj, 2));
+        TRYCU(cudaMemcpyAsync(f.view_proj, vp, sizeof(vp), cudaMemcpyHostToDevice, r->stream));
+        TRYCU(cudaStreamSynchronize(r->stream));               // vp is a stack object
+    }
+
     // ---- camera
     const ptb_camera& c = scene->camera;
     f.cam.res_x = W; f.cam.res_y = H;
@@ -435,19 +491,25 @@ int ptb_clear_accumulators(ptb_renderer* r) {
 
 int ptb_resolve(ptb_renderer* r, void* dst, int32_t format, int32_t iteration, int32_t dst_on_device) {
     if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_resolve: null argument");
-    if (format < PTB_IMG_SUM_RGB32F || format > PTB_IMG_RGBA8) return fail(PTB_ERR_INVALID, "ptb_resolve: unknown format");
-    if (format != PTB_IMG_SUM_RGB32F && iteration < 1) return fail(PTB_ERR_INVALID, "ptb_resolve: iteration must be >= 1");
+    if (format < PTB_IMG_SUM_RGB32F || format > PTB_IMG_VIEW_MOTION) return fail(PTB_ERR_INVALID, "ptb_resolve: unknown format");
+    const bool view = format >= PTB_IMG_VIEW_NORMALS;
+    if (view && !r->gbuffer) return fail(PTB_ERR_STATE, "ptb_resolve: G-buffer views need ptb_config.gbuffer = 1");
+    if (!view && format != PTB_IMG_SUM_RGB32F && iteration < 1) return fail(PTB_ERR_INVALID, "ptb_resolve: iteration must be >= 1");
     CU(cudaSetDevice(r->device));
     const size_t P = (size_t)r->frame.num_paths;
-    const size_t bytes = P * (format == PTB_IMG_RGBA8 ? 4 : 12);
+    const size_t bytes = P * ((format == PTB_IMG_RGBA8 || view) ? 4 : 12);
+    auto run = [&](void* out) {
+        if (view) return launch_view(r->gb, (int)P, out, format - PTB_IMG_VIEW_NORMALS + 1, r->stream);
+        return launch_resolve(r->frame, out, format, iteration, r->stream);
+    };
     if (dst_on_device) {
-        r->kernel_launches += launch_resolve(r->frame, dst, format, iteration, r->stream);
+        r->kernel_launches += run(dst);
         CU(cudaGetLastError());
         return PTB_OK;
     }
     int rc = ensure_scratch(r, bytes);
     if (rc) return rc;
-    r->kernel_launches += launch_resolve(r->frame, r->scratch, format, iteration, r->stream);
+    r->kernel_launches += run(r->scratch);
     CU(cudaMemcpyAsync(dst, r->scratch, bytes, cudaMemcpyDeviceToHost, r->stream));
     CU(cudaStreamSynchronize(r->stream));
     return check_device_error(r);
@@ -460,6 +522,46 @@ int ptb_get_accumulators(ptb_renderer* r, float* direct, float* indirect) {
     const size_t bytes = 3 * (size_t)r->frame.num_paths * sizeof(float);
     if (direct) CU(cudaMemcpy(direct, r->frame.direct, bytes, cudaMemcpyDeviceToHost));
     if (indirect) CU(cudaMemcpy(indirect, r->frame.indirect, bytes, cudaMemcpyDeviceToHost));
+    return check_device_error(r);
+}
+
+int ptb_get_gbuffer(ptb_renderer* r, int32_t which, void* dst, size_t bytes) {
+    if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_gbuffer: null argument");
+    if (!r->gbuffer) return fail(PTB_ERR_STATE, "ptb_get_gbuffer: renderer was created without ptb_config.gbuffer");
+    const size_t P = (size_t)r->frame.num_paths;
+    const void* src = nullptr; size_t elem = 0;
+    switch (which) {
+        case PTB_GB_DEPTH: src = r->gb.depth; elem = 4; break;
+        case PTB_GB_NORMAL_MATID: src = r->gb.normal_matid; elem = 16; break;
+        case PTB_GB_ALBEDO: src = r->gb.albedo; elem = 16; break;
+        case PTB_GB_MOTION: src = r->gb.motion; elem = 8; break;
+        default: return fail(PTB_ERR_INVALID, "ptb_get_gbuffer: unknown buffer");
+    }
+    if (bytes < P * elem) return fail(PTB_ERR_INVALID, "ptb_get_gbuffer: destination too small");
+    CU(cudaSetDevice(r->device));
+    CU(cudaStreamSynchronize(r->stream));
+    CU(cudaMemcpy(dst, src, P * elem, cudaMemcpyDeviceToHost));
+    return check_device_error(r);
+}
+
+int ptb_visualize_lbvh(ptb_renderer* r, void* dst, int32_t format, int32_t dst_on_device) {
+    if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_visualize_lbvh: null argument");
+    if (format != PTB_IMG_SUM_RGB32F && format != PTB_IMG_STEPS_I32) return fail(PTB_ERR_INVALID, "ptb_visualize_lbvh: format must be PTB_IMG_SUM_RGB32F or PTB_IMG_STEPS_I32");
+    CU(cudaSetDevice(r->device));
+    const size_t P = (size_t)r->frame.num_paths;
+    const size_t bytes = P * (format == PTB_IMG_SUM_RGB32F ? 12 : 4);
+    void* out = dst;
+    if (!dst_on_device) {
+        int rc = ensure_scratch(r, bytes);
+        if (rc) return rc;
+        out = r->scratch;
+    }
+    r->kernel_launches += launch_bvh_heatmap(r->frame, format == PTB_IMG_SUM_RGB32F ? (float*)out : nullptr,
+                                             format == PTB_IMG_STEPS_I32 ? (int*)out : nullptr, r->stream);
+    CU(cudaGetLastError());
+    if (dst_on_device) return PTB_OK;
+    CU(cudaMemcpyAsync(dst, r->scratch, bytes, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
     return check_device_error(r);
 }
 

@@ -107,11 +107,12 @@ class Scene:
 class Renderer:
     """An opaque ptb_renderer: PathtraceInit / Pathtrace / PathtraceFree on a handle."""
 
-    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True):
+    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False):
         cfg = capi.Config()
         lib.ptb_config_default(C.byref(cfg))
         cfg.device, cfg.trace_depth, cfg.rank, cfg.world, cfg.stripe_rows = device, trace_depth, rank, world, stripe_rows
         cfg.use_graph = 1 if use_graph else 0
+        cfg.gbuffer = 1 if gbuffer else 0
         self._h = C.c_void_p()
         check(lib.ptb_init(scene._h, C.byref(cfg), C.byref(self._h)))
         t = capi.TileInfo()
@@ -132,11 +133,25 @@ class Renderer:
 
     def resolve(self, iteration, fmt=capi.IMG_MEAN_RGB32F, out=None):
         """(direct + indirect) / iteration for the owned pixels, into a host array."""
-        if fmt == capi.IMG_RGBA8:
+        if fmt == capi.IMG_RGBA8 or fmt >= capi.IMG_VIEW_NORMALS:
             out = np.empty((self.owned_pixels, 4), dtype=np.uint8) if out is None else out
         else:
             out = np.empty((self.owned_pixels, 3), dtype=np.float32) if out is None else out
         check(lib.ptb_resolve(self._h, ptr(out), fmt, iteration, 0))
+        return out
+
+    def gbuffer(self, which):
+        """First-bounce G-buffer of the last frame: 'depth' (P,), 'normal_matid' (P,4), 'albedo' (P,4), 'motion' (P,2)."""
+        idx, shape = {"depth": (capi.GB_DEPTH, (self.owned_pixels,)), "normal_matid": (capi.GB_NORMAL_MATID, (self.owned_pixels, 4)),
+                      "albedo": (capi.GB_ALBEDO, (self.owned_pixels, 4)), "motion": (capi.GB_MOTION, (self.owned_pixels, 2))}[which]
+        out = np.empty(shape, dtype=np.float32)
+        check(lib.ptb_get_gbuffer(self._h, idx, ptr(out), out.nbytes))
+        return out
+
+    def visualize_lbvh(self, steps=False):
+        """LBVH traversal-cost heat map (VisualizeLBVH): float32 (P,3) colours, or int32 (P,) node visits."""
+        out = np.empty((self.owned_pixels,), dtype=np.int32) if steps else np.empty((self.owned_pixels, 3), dtype=np.float32)
+        check(lib.ptb_visualize_lbvh(self._h, ptr(out), capi.IMG_STEPS_I32 if steps else capi.IMG_SUM_RGB32F, 0))
         return out
 
     def resolve_device(self, device_ptr, iteration, fmt=capi.IMG_MEAN_RGB32F):

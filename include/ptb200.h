@@ -134,7 +134,9 @@ typedef struct ptb_config {
      * to a 1-GPU render.  world <= 1 renders the full frame. */
     int32_t rank, world, stripe_rows;
     int32_t use_graph;       /* 1: replay the frame as a CUDA graph (default); 0: plain launches */
-    int32_t reserved[8];
+    int32_t gbuffer;         /* 1: keep the first-bounce G-buffer the reference's Logic writes every frame (depth, normal +
+                                material id, albedo, motion; src/kernels/logic.cu:66-73,119-138); 0 (default): skip it */
+    int32_t reserved[7];
 } ptb_config;
 void ptb_config_default(ptb_config* cfg);
 
@@ -167,9 +169,21 @@ int ptb_set_stream(ptb_renderer* r, void* cuda_stream);
  * PTB_IMG_RGBA8      : gamma 1/2.2, x255, clamp, alpha 255       (:80,112-115)
  * dst holds owned_pixels (see ptb_get_tile_info) elements when the renderer is a tile of a
  * multi-GPU frame, else width*height.  dst_on_device != 0: dst is a device pointer (written on
- * the renderer's stream, asynchronous); else a host pointer (synchronous). */
-enum { PTB_IMG_SUM_RGB32F = 0, PTB_IMG_MEAN_RGB32F = 1, PTB_IMG_RGBA8 = 2 };
+ * the renderer's stream, asynchronous); else a host pointer (synchronous).
+ * PTB_IMG_VIEW_*     : the other display modes of that kernel (:82-109) as RGBA8, from the G-buffer
+ *                      (needs ptb_config.gbuffer): normals*0.5+0.5, 1-depth/500, albedo, motion*100+0.5 */
+enum { PTB_IMG_SUM_RGB32F = 0, PTB_IMG_MEAN_RGB32F = 1, PTB_IMG_RGBA8 = 2,
+       PTB_IMG_VIEW_NORMALS = 3, PTB_IMG_VIEW_DEPTH = 4, PTB_IMG_VIEW_ALBEDO = 5, PTB_IMG_VIEW_MOTION = 6,
+       PTB_IMG_STEPS_I32 = 7 /* ptb_visualize_lbvh only: int32 node visits per pixel */ };
 int ptb_resolve(ptb_renderer* r, void* dst, int32_t format, int32_t iteration, int32_t dst_on_device);
+/* First-bounce G-buffer of the last rendered frame, one element per owned pixel (needs ptb_config.gbuffer):
+ * WavefrontPathTracerState::d_depth / d_normal_matid / d_albedo / d_motion_vectors (src/wavefront_internal.cu:286-300). */
+enum { PTB_GB_DEPTH = 0 /* float */, PTB_GB_NORMAL_MATID = 1 /* float4 */, PTB_GB_ALBEDO = 2 /* float4 */, PTB_GB_MOTION = 3 /* float2 */ };
+int ptb_get_gbuffer(ptb_renderer* r, int32_t which, void* dst, size_t bytes);
+/* VisualizeLBVH (src/bvh.cu:518-640): per pixel, the number of LBVH nodes an un-jittered camera ray visits, as the
+ * reference's blue-to-red colour (PTB_IMG_SUM_RGB32F, float3, = its d_final_image) or as the raw count
+ * (PTB_IMG_STEPS_I32).  Replaces the GL "Show BVH Heatmap" view (src/preview.cpp:159). */
+int ptb_visualize_lbvh(ptb_renderer* r, void* dst, int32_t format, int32_t dst_on_device);
 /* Raw accumulators (WavefrontPathTracerState::d_direct_image / d_indirect_image,
  * src/wavefront_internal.h:26-27) copied to host, 3 floats per owned pixel; either may be NULL. */
 int ptb_get_accumulators(ptb_renderer* r, float* direct, float* indirect);

@@ -190,13 +190,13 @@ static double now_s() {
 int main(int argc, char** argv) {
     if (argc < 3) {
         fprintf(stderr,
-            "usage: refdump SCENE.json OUTDIR [--iters N] [--stages] [--selfcheck] [--bench K W] [--mega] [--no-dump]\n");
+            "usage: refdump SCENE.json OUTDIR [--iters N] [--stages] [--selfcheck] [--bench K W] [--mega] [--no-dump] [--views]\n");
         return 1;
     }
     std::string scene_file = argv[1];
     g_out = argv[2];
     int iters = 1, bench_k = 0, bench_w = 0;
-    bool stages = false, selfcheck = false, mega = false, no_dump = false;
+    bool stages = false, selfcheck = false, mega = false, no_dump = false, views = false;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         if (a == "--iters" && i + 1 < argc) iters = atoi(argv[++i]);
@@ -204,6 +204,7 @@ int main(int argc, char** argv) {
         else if (a == "--selfcheck") selfcheck = true;
         else if (a == "--mega") mega = true;
         else if (a == "--no-dump") no_dump = true;
+        else if (a == "--views") views = true;
         else if (a == "--bench" && i + 2 < argc) { bench_k = atoi(argv[++i]); bench_w = atoi(argv[++i]); }
     }
     mkdir(g_out.c_str(), 0777);
@@ -277,6 +278,29 @@ int main(int argc, char** argv) {
     cudaDeviceSynchronize();
     dump_dev("direct", st->d_direct_image, sizeof(glm::vec3) * P);
     dump_dev("indirect", st->d_indirect_image, sizeof(glm::vec3) * P);
+    if (views) {
+        // first-bounce G-buffer of the last frame (written by the reference's Logic, src/kernels/logic.cu:66-73,119-138)
+        dump_dev("gb_depth", st->d_depth, sizeof(float) * P);
+        dump_dev("gb_normal_matid", st->d_normal_matid, sizeof(float4) * P);
+        dump_dev("gb_albedo", st->d_albedo, sizeof(float4) * P);
+        dump_dev("gb_motion", st->d_motion_vectors, sizeof(float2) * P);
+        dump_raw("view_proj", &st->view_proj_mat, sizeof(glm::mat4));
+        // the display modes of the reference's own SendImageToPBOKernel into a plain device buffer
+        uchar4* pbo = nullptr;
+        cudaMalloc(&pbo, sizeof(uchar4) * P);
+        const dim3 bs(8, 8), grid((cam.resolution.x + 7) / 8, (cam.resolution.y + 7) / 8);
+        for (int mode = 0; mode <= 4; mode++) {
+            pathtrace_wavefront::SendImageToPBOKernel<<<grid, bs>>>(pbo, cam.resolution, iters, mode, false, st->d_final_image,
+                st->d_direct_image, st->d_indirect_image, st->d_normal_matid, st->d_depth, st->d_albedo, st->d_motion_vectors);
+            char name[16]; snprintf(name, sizeof(name), "view%d", mode);
+            dump_dev(name, pbo, sizeof(uchar4) * P);
+        }
+        cudaFree(pbo);
+        // BVH heat map: the reference's VisualizeLBVH into its final image buffer (src/pathtrace_wavefront.cu:244-256)
+        VisualizeLBVH(st->d_final_image, cam.resolution.x, cam.resolution.y, cam, st->d_bvh_data, st->d_mesh_data.num_triangles);
+        cudaDeviceSynchronize();
+        dump_dev("bvh_heatmap", st->d_final_image, sizeof(glm::vec3) * P);
+    }
     cudaError_t e = cudaGetLastError();
     printf("REFDUMP {\"iters\": %d, \"pixels\": %d, \"cuda\": \"%s\"}\n", iters, P, cudaGetErrorString(e));
     pathtrace_wavefront::PathtraceFree();

@@ -283,3 +283,39 @@ def test_stress_10m_lbvh_and_raycast_vs_oracle():
     a = r.resolve(2)
     assert np.isfinite(a).all() and a.max() > 0
     r.free()
+
+
+# ------------------------------------------------------------------------------------------ headless views
+@pytest.mark.parametrize("which,iters", [("cornell", 1), ("sponza_small", 1), ("sponza_small", 2)])
+def test_gbuffer_views_and_heatmap_vs_reference(which, iters, sponza_small, tmp_path):
+    """What the reference only shows through its GL preview: the first-bounce G-buffer its Logic stage writes, the
+    display modes of SendImageToPBOKernel, and the VisualizeLBVH heat map -- against the reference's own kernels."""
+    _need_ref()
+    scene_json = scenegen.cornell(str(tmp_path / "c"), res=(200, 160)) if which == "cornell" else sponza_small
+    d = str(tmp_path / "ref")
+    par.run_refdump(scene_json, d, iters=iters, stages=False, views=True)
+    ref = par.RefDump(d)
+    r = ptb.Renderer(ptb.Scene(scene_json), gbuffer=True)
+    r.render(1, iters)
+    # iteration 1 sees prev_view_proj = identity (large motion); later ones prev == current, where the reference's
+    # fma(u_cur, res, -(u_prev * res)) leaves the rounding error of the product, not an exact zero -- so do we
+    assert _bits(r.gbuffer("depth"), ref.load("gb_depth", "<f4"))
+    assert _bits(r.gbuffer("normal_matid"), ref.load("gb_normal_matid", "<f4", 4))
+    assert _bits(r.gbuffer("albedo"), ref.load("gb_albedo", "<f4", 4))
+    mine, theirs = r.gbuffer("motion"), ref.load("gb_motion", "<f4", 2)
+    assert _bits(mine, theirs), float(np.abs(mine - theirs).max())
+    if iters > 1:
+        assert np.abs(mine).max() < 1e-3
+    assert np.array_equal(r.resolve(iters, capi.IMG_RGBA8), ref.load("view0", "u1", 4))
+    for k, fmt in enumerate((capi.IMG_VIEW_NORMALS, capi.IMG_VIEW_DEPTH, capi.IMG_VIEW_ALBEDO, capi.IMG_VIEW_MOTION), 1):
+        assert np.array_equal(r.resolve(iters, fmt), ref.load(f"view{k}", "u1", 4)), k
+    heat = ref.load("bvh_heatmap", "<f4", 3)
+    assert _bits(r.visualize_lbvh(), heat)
+    steps = r.visualize_lbvh(steps=True)
+    assert steps.min() >= 0 and steps.max() > 1
+    r.free()
+    plain = ptb.Renderer(ptb.Scene(scene_json))
+    with pytest.raises(capi.PtbError) as e:
+        plain.gbuffer("depth")
+    assert e.value.code == capi.ERR_STATE
+    plain.free()
