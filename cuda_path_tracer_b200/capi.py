@@ -22,6 +22,7 @@ OK, ERR_INVALID, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_STATE = 0, -1
 IMG_SUM_RGB32F, IMG_MEAN_RGB32F, IMG_RGBA8 = 0, 1, 2
 IMG_VIEW_NORMALS, IMG_VIEW_DEPTH, IMG_VIEW_ALBEDO, IMG_VIEW_MOTION, IMG_STEPS_I32 = 3, 4, 5, 6, 7
 GB_DEPTH, GB_NORMAL_MATID, GB_ALBEDO, GB_MOTION = 0, 1, 2, 3
+SAVE_GAMMA, SAVE_FLIP_X = 1, 2
 STAGE_RAYGEN, STAGE_TRACE, STAGE_LOGIC, STAGE_SHADE = 0, 1, 2, 3
 Q_EXTENSION, Q_SHADOW, Q_PBR, Q_DIFFUSE, Q_REFLECTION, Q_REFRACTION = range(6)
 
@@ -86,6 +87,7 @@ SIGNATURES = {
     "ptb_render": (C.c_int, [P, C.c_int32]),
     "ptb_render_many": (C.c_int, [P, C.c_int32, C.c_int32]),
     "ptb_clear_accumulators": (C.c_int, [P]),
+    "ptb_save_image": (C.c_int, [C.c_char_p, P, C.c_int32, C.c_int32, C.c_float, C.c_int32]),
     "ptb_get_gbuffer": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
     "ptb_visualize_lbvh": (C.c_int, [P, P, C.c_int32, C.c_int32]),
     "ptb_sync": (C.c_int, [P]),

@@ -4,6 +4,7 @@
 // file restates just those: binary PNM (P5/P6, maxval 255), BMP (24/32 bpp BI_RGB), TGA
 // (type 2/3, 8/24/32 bpp) and Radiance RGBE .hdr (flat and new-style RLE scanlines).
 // RGBE -> float follows stb: value = mantissa * 2^(e - 136), all-zero when e == 0.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -183,6 +184,99 @@ bool load_image_hdr(const std::string& path, int& w, int& h, std::vector<float>&
         }
         for (int x = 0; x < w; x++) rgbe_to_float(&scan[(size_t)x * 4], &rgb[((size_t)y * w + x) * 3]);
     }
+    return true;
+}
+
+}  // namespace ptb
+
+// ---- writers (the reference's Image::savePNG / saveHDR, src/image.cpp:22-49, via stb_image_write) ---------------
+namespace ptb {
+
+static uint32_t crc32_of(const uint8_t* p, size_t n, uint32_t crc = 0) {
+    static uint32_t table[256];
+    static bool ready = false;
+    if (!ready) {
+        for (uint32_t i = 0; i < 256; i++) {
+            uint32_t c = i;
+            for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+            table[i] = c;
+        }
+        ready = true;
+    }
+    crc = ~crc;
+    for (size_t i = 0; i < n; i++) crc = table[(crc ^ p[i]) & 0xff] ^ (crc >> 8);
+    return ~crc;
+}
+
+static void be32(std::vector<uint8_t>& v, uint32_t x) { v.push_back(x >> 24); v.push_back(x >> 16); v.push_back(x >> 8); v.push_back(x); }
+
+static void png_chunk(std::vector<uint8_t>& out, const char* type, const std::vector<uint8_t>& data) {
+    be32(out, (uint32_t)data.size());
+    size_t start = out.size();
+    out.insert(out.end(), type, type + 4);
+    out.insert(out.end(), data.begin(), data.end());
+    be32(out, crc32_of(out.data() + start, out.size() - start));
+}
+
+// 8-bit RGB PNG, one filter-0 scanline per row, zlib stream of stored (uncompressed) deflate blocks: valid for every
+// PNG reader and needs no compression library.
+bool save_png_rgb8(const std::string& path, const uint8_t* rgb, int w, int h, std::string& err) {
+    if (w <= 0 || h <= 0) { err = "empty image"; return false; }
+    std::vector<uint8_t> raw;
+    raw.reserve((size_t)h * (3 * (size_t)w + 1));
+    for (int y = 0; y < h; y++) {
+        raw.push_back(0);
+        raw.insert(raw.end(), rgb + 3 * (size_t)w * y, rgb + 3 * (size_t)w * (y + 1));
+    }
+    std::vector<uint8_t> z;
+    z.push_back(0x78); z.push_back(0x01);
+    uint32_t a = 1, b = 0;   // adler32
+    size_t pos = 0;
+    while (pos < raw.size()) {
+        size_t n = std::min<size_t>(65535, raw.size() - pos);
+        z.push_back(pos + n == raw.size() ? 1 : 0);
+        z.push_back(n & 0xff); z.push_back(n >> 8); z.push_back(~n & 0xff); z.push_back((~n >> 8) & 0xff);
+        for (size_t i = 0; i < n; i++) { a = (a + raw[pos + i]) % 65521; b = (b + a) % 65521; }
+        z.insert(z.end(), raw.begin() + pos, raw.begin() + pos + n);
+        pos += n;
+    }
+    be32(z, (b << 16) | a);
+    std::vector<uint8_t> out = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    std::vector<uint8_t> ihdr;
+    be32(ihdr, (uint32_t)w); be32(ihdr, (uint32_t)h);
+    ihdr.push_back(8); ihdr.push_back(2); ihdr.push_back(0); ihdr.push_back(0); ihdr.push_back(0);
+    png_chunk(out, "IHDR", ihdr);
+    png_chunk(out, "IDAT", z);
+    png_chunk(out, "IEND", {});
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) { err = "cannot open " + path; return false; }
+    bool ok = fwrite(out.data(), 1, out.size(), f) == out.size();
+    fclose(f);
+    if (!ok) err = "short write to " + path;
+    return ok;
+}
+
+// Radiance .hdr, flat RGBE scanlines (stb_image_write's float -> RGBE rule: frexp of the largest channel).
+bool save_hdr_rgb32f(const std::string& path, const float* rgb, int w, int h, std::string& err) {
+    if (w <= 0 || h <= 0) { err = "empty image"; return false; }
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) { err = "cannot open " + path; return false; }
+    fprintf(f, "#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y %d +X %d\n", h, w);
+    std::vector<uint8_t> row(4 * (size_t)w);
+    for (int y = 0; y < h; y++) {
+        for (int x = 0; x < w; x++) {
+            const float* p = rgb + 3 * ((size_t)y * w + x);
+            float m = std::max(p[0], std::max(p[1], p[2]));
+            uint8_t* o = &row[4 * (size_t)x];
+            if (!(m >= 1e-32f)) { o[0] = o[1] = o[2] = o[3] = 0; continue; }
+            int e;
+            float scale = std::frexp(m, &e) * 256.0f / m;
+            o[0] = (uint8_t)(p[0] * scale); o[1] = (uint8_t)(p[1] * scale); o[2] = (uint8_t)(p[2] * scale);
+            o[3] = (uint8_t)(e + 128);
+        }
+        if (fwrite(row.data(), 1, row.size(), f) != row.size()) { fclose(f); err = "short write to " + path; return false; }
+    }
+    fclose(f);
     return true;
 }
 

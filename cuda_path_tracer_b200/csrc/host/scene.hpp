@@ -78,5 +78,7 @@ void derive_camera(ptb_camera& cam, float fovy_deg);
 // also reads (PNM P5/P6, BMP 24/32, TGA 24/32 uncompressed, Radiance .hdr flat + RLE).
 bool load_image_u8(const std::string& path, int& w, int& h, int& channels, std::vector<uint8_t>& px, std::string& err);
 bool load_image_hdr(const std::string& path, int& w, int& h, std::vector<float>& rgb, std::string& err);
+bool save_png_rgb8(const std::string& path, const uint8_t* rgb, int w, int h, std::string& err);
+bool save_hdr_rgb32f(const std::string& path, const float* rgb, int w, int h, std::string& err);
 
 }  // namespace ptb

@@ -1,5 +1,8 @@
 // scene_api.cpp -- the ptb_scene_* half of the C ABI (include/ptb200.h).  Pure host code.
 // Replaces `class Scene` (reference src/scene.h:51-92, src/scene.cpp:45-631).
+#include <vector>
+#include <cmath>
+#include <algorithm>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -118,6 +121,39 @@ int ptb_scene_get_info(const ptb_scene* s, ptb_scene_info* out) {
     out->pdf_map_id = s->env.pdf_map_id;
     out->light_total_area = s->light_total_area;
     return PTB_OK;
+}
+
+int ptb_save_image(const char* path, const float* rgb, int32_t width, int32_t height, float scale, int32_t flags) {
+    if (!path || !rgb) return fail(PTB_ERR_INVALID, "ptb_save_image: null argument");
+    if (width <= 0 || height <= 0) return fail(PTB_ERR_INVALID, "ptb_save_image: empty image");
+    std::string p(path);
+    const bool png = p.size() > 4 && p.compare(p.size() - 4, 4, ".png") == 0;
+    const bool hdr = p.size() > 4 && p.compare(p.size() - 4, 4, ".hdr") == 0;
+    if (!png && !hdr) return fail(PTB_ERR_INVALID, "ptb_save_image: path must end in .png or .hdr");
+    const size_t n = (size_t)width * height;
+    std::vector<float> img(3 * n);
+    const float inv_gamma = 1.0f / 2.2f;
+    for (int y = 0; y < height; y++)
+        for (int x = 0; x < width; x++) {
+            const float* s = rgb + 3 * ((size_t)y * width + x);
+            int dx = (flags & PTB_SAVE_FLIP_X) ? width - 1 - x : x;        // img.setPixel(width - 1 - x, y, ...), src/main.cpp:259
+            float* d = &img[3 * ((size_t)y * width + dx)];
+            for (int c = 0; c < 3; c++) {
+                float v = s[c] * scale;                                      // renderState->image[index] / samples, :254
+                if (flags & PTB_SAVE_GAMMA) v = std::pow(std::max(0.0f, v), inv_gamma);   // :256-258
+                d[c] = v;
+            }
+        }
+    std::string err;
+    bool ok;
+    if (hdr) {
+        ok = ptb::save_hdr_rgb32f(p, img.data(), width, height, err);
+    } else {
+        std::vector<uint8_t> bytes(3 * n);                                   // Image::savePNG, src/image.cpp:22-43
+        for (size_t i = 0; i < 3 * n; i++) bytes[i] = (uint8_t)(std::min(std::max(img[i], 0.0f), 1.0f) * 255.0f);
+        ok = ptb::save_png_rgb8(p, bytes.data(), width, height, err);
+    }
+    return ok ? PTB_OK : fail(PTB_ERR_IO, "ptb_save_image: " + err);
 }
 
 int ptb_scene_get_camera(const ptb_scene* s, ptb_camera* out) {

@@ -247,6 +247,13 @@ class Renderer:
             pass
 
 
+def save_image(path, rgb, width, height, scale=1.0, gamma=False, flip_x=False):
+    """Image::savePNG / saveHDR (+ main.cpp's saveImage transform): rgb float32 [height*width, 3]; .png or .hdr."""
+    rgb = np.ascontiguousarray(rgb, dtype=np.float32).reshape(height * width, 3)
+    flags = (capi.SAVE_GAMMA if gamma else 0) | (capi.SAVE_FLIP_X if flip_x else 0)
+    check(lib.ptb_save_image(path.encode(), ptr(rgb), width, height, float(scale), flags))
+
+
 def build_lbvh(pos4, indices_matid4, device=0):
     """BuildLBVH (src/bvh.h:7) on host arrays; returns the reference-layout arrays and the build time."""
     pos4 = np.ascontiguousarray(pos4, dtype=np.float32).reshape(-1, 4)

@@ -96,6 +96,14 @@ int ptb_scene_set_camera(ptb_scene* s, const int32_t resolution[2], float fovy_d
                          const float eye[3], const float look_at[3], const float up[3], int32_t trace_depth);
 void ptb_scene_free(ptb_scene* s);
 
+/* Image::savePNG / Image::saveHDR (src/image.cpp:22-49) with the transform of main.cpp's saveImage()
+ * (src/main.cpp:239-262) as options.  rgb: float3[height*width], row-major.  Every channel is multiplied by
+ * `scale` (the reference divides by the sample count), then PTB_SAVE_GAMMA applies pow(max(0, c), 1/2.2) and
+ * PTB_SAVE_FLIP_X mirrors the columns (the reference writes pixel x to width-1-x).  The extension picks the
+ * format: .png (8-bit RGB, clamp to [0,1] x 255, truncated) or .hdr (Radiance RGBE).  Pure host code. */
+enum { PTB_SAVE_GAMMA = 1, PTB_SAVE_FLIP_X = 2 };
+int ptb_save_image(const char* path, const float* rgb, int32_t width, int32_t height, float scale, int32_t flags);
+
 typedef struct ptb_scene_info {
     int32_t num_vertices, num_triangles, num_materials, num_lights, num_textures;
     int32_t width, height, trace_depth, iterations;

@@ -120,3 +120,44 @@ def test_product_does_not_touch_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")) or f == "Makefile":
                 text = open(os.path.join(dp, f), errors="replace").read()
                 assert "libptoracle" not in text and "_oracle" not in text and "refdump" not in text.replace("oracle/_ref/refdump) and this library", ""), os.path.join(dp, f)
+
+
+def test_save_image_png_and_hdr(tmp_path):
+    """Image::savePNG / saveHDR + saveImage()'s scale / gamma / mirror (src/image.cpp:22-49, src/main.cpp:239-262)."""
+    import struct
+    import zlib
+    w, h = 37, 11
+    rng = np.random.RandomState(5)
+    img = rng.uniform(-0.2, 3.0, (h * w, 3)).astype(np.float32)
+    png = str(tmp_path / "a.png")
+    ptb.save_image(png, img, w, h, scale=0.5, gamma=True, flip_x=True)
+    raw = open(png, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, ihdr = 8, b"", None
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(typ + body)
+        if typ == b"IHDR":
+            ihdr = struct.unpack(">IIBBBBB", body)
+        if typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert ihdr == (w, h, 8, 2, 0, 0, 0)
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)
+    assert not rows[:, 0].any()
+    got = rows[:, 1:].reshape(h, w, 3)
+    v = np.maximum(np.float32(0), img.reshape(h, w, 3) * np.float32(0.5)) ** np.float32(1 / 2.2)
+    want = (np.clip(v, 0, 1) * np.float32(255)).astype(np.uint8)[:, ::-1]
+    assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and (got != want).mean() < 0.01   # powf vs numpy at the truncation edge
+    hdr = str(tmp_path / "a.hdr")
+    pos_img = np.abs(img)
+    ptb.save_image(hdr, pos_img, w, h)
+    data = open(hdr, "rb").read()
+    head, body = data.split(b"\n\n", 1)
+    assert head.startswith(b"#?RADIANCE") and body.startswith(b"-Y %d +X %d\n" % (h, w))
+    px = np.frombuffer(body.split(b"\n", 1)[1], np.uint8).reshape(h * w, 4).astype(np.float32)
+    back = px[:, :3] * np.exp2(px[:, 3:4] - 136)
+    assert np.all(np.abs(back - pos_img) <= pos_img.max(1, keepdims=True) / 128 + 1e-6)
+    with pytest.raises(capi.PtbError):
+        ptb.save_image(str(tmp_path / "a.jpg"), img, w, h)
