@@ -21,6 +21,7 @@ class PtbError(RuntimeError):
 OK, ERR_INVALID, ERR_IO, ERR_PARSE, ERR_CUDA, ERR_UNSUPPORTED, ERR_STATE = 0, -1, -2, -3, -4, -5, -6
 IMG_SUM_RGB32F, IMG_MEAN_RGB32F, IMG_RGBA8 = 0, 1, 2
 IMG_VIEW_NORMALS, IMG_VIEW_DEPTH, IMG_VIEW_ALBEDO, IMG_VIEW_MOTION, IMG_STEPS_I32 = 3, 4, 5, 6, 7
+IMG_DENOISED_RGB32F, IMG_DENOISED_RGBA8 = 8, 9
 GB_DEPTH, GB_NORMAL_MATID, GB_ALBEDO, GB_MOTION = 0, 1, 2, 3
 SAVE_GAMMA, SAVE_FLIP_X = 1, 2
 STAGE_RAYGEN, STAGE_TRACE, STAGE_LOGIC, STAGE_SHADE = 0, 1, 2, 3
@@ -54,7 +55,7 @@ class SceneInfo(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("trace_depth", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("denoiser", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class TileInfo(C.Structure):

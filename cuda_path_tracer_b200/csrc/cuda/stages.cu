@@ -263,14 +263,19 @@ __global__ void __launch_bounds__(256) k_resolve(const float* __restrict__ direc
                                                  void* dst, int format, int iter) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    Vec3 c(direct[3 * (size_t)i] + indirect[3 * (size_t)i], direct[3 * (size_t)i + 1] + indirect[3 * (size_t)i + 1],
-         direct[3 * (size_t)i + 2] + indirect[3 * (size_t)i + 2]);
+    Vec3 c;
+    if (indirect) {
+        c = Vec3(direct[3 * (size_t)i] + indirect[3 * (size_t)i], direct[3 * (size_t)i + 1] + indirect[3 * (size_t)i + 1],
+                 direct[3 * (size_t)i + 2] + indirect[3 * (size_t)i + 2]);
+    } else {   // denoised final image: shown as it is (SendImageToPBOKernel with denoiserOn, src/pathtrace_wavefront.cu:69-71)
+        c = Vec3(direct[3 * (size_t)i], direct[3 * (size_t)i + 1], direct[3 * (size_t)i + 2]);
+    }
     if (format == PTB_IMG_SUM_RGB32F) {
         float* o = (float*)dst + 3 * (size_t)i;
         o[0] = c.x; o[1] = c.y; o[2] = c.z;
         return;
     }
-    c = c / (float)iter;
+    if (indirect) c = c / (float)iter;
     if (format == PTB_IMG_MEAN_RGB32F) {
         float* o = (float*)dst + 3 * (size_t)i;
         o[0] = c.x; o[1] = c.y; o[2] = c.z;
@@ -320,6 +325,10 @@ int launch_frame_end(const FrameDev& f, const LaunchCfg&, cudaStream_t s) {
 }
 int launch_resolve(const FrameDev& f, void* dst, int format, int iteration, cudaStream_t s) {
     k_resolve<<<(f.num_paths + 255) / 256, 256, 0, s>>>(f.direct, f.indirect, f.num_paths, dst, format, iteration);
+    return 1;
+}
+int launch_resolve_final(const float* final_image, int n, void* dst, int format, cudaStream_t s) {
+    k_resolve<<<(n + 255) / 256, 256, 0, s>>>(final_image, nullptr, n, dst, format, 1);
     return 1;
 }
 

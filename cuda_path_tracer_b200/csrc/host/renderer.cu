@@ -3,6 +3,7 @@
 // Replaces pathtrace_wavefront::{PathtraceInit, Pathtrace, PathtraceFree} (reference
 // src/pathtrace_wavefront.cu:144-413) and WavefrontPathTracerState (src/wavefront_internal.cu).
 #include <cmath>
+#include <utility>
 #include <cstdlib>
 #include <cuda_runtime.h>
 
@@ -41,6 +42,9 @@ struct ptb_renderer {
     float last_batch_ms = 0.0f;
     bool gbuffer = false;                 // ptb_config.gbuffer: first-bounce G-buffer kept every frame
     GBufferDev gb{};
+    bool denoiser = false;                // ptb_config.denoiser: SVGF over a 1-spp frame, every frame
+    SvgfDev svgf{};
+    std::vector<std::pair<void*, size_t>> svgf_state;   // buffers zeroed when iteration 1 restarts the history
     size_t device_bytes = 0;
 
     // frame graph
@@ -168,6 +172,8 @@ static Mat4 camera_view_proj(const ptb_camera& c) {
 static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
     const FrameDev& f = r->frame;
     int n = 0;
+    // with the denoiser every frame is a fresh 1-spp estimate (src/pathtrace_wavefront.cu:231-236)
+    if (r->denoiser) n += launch_clear_accumulators(f, s);
     n += launch_raygen(f, r->launch, s);
     for (int b = 0; b < f.trace_depth; b++) {
         // whole frames run Logic inside the extension RayCast kernel; the staged API keeps the stages apart
@@ -192,6 +198,7 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
         if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
     }
+    if (r->denoiser) n += launch_svgf(f, r->svgf, r->gb, s);   // reads *f.iteration: before frame_end advances it
     n += launch_frame_end(f, r->launch, s);
     return n;
 }
@@ -389,7 +396,8 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
 
     // ---- first-bounce G-buffer (initSVGF buffers, src/wavefront_internal.cu:286-300), on request
     f.view_proj = nullptr;
-    if (cfg.gbuffer) {
+    if (cfg.denoiser && cfg.world > 1) { ptb_free(r); return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the denoiser filters across rows; it needs the whole frame on one GPU (world == 1)"); }
+    if (cfg.gbuffer || cfg.denoiser) {
         r->gbuffer = true;
         TRY(dev_alloc(r, r->gb.depth, P));
         TRY(dev_alloc(r, r->gb.normal_matid, P));
@@ -406,6 +414,23 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         TRY(dev_alloc(r, f.view_proj, 2));
         TRYCU(cudaMemcpyAsync(f.view_proj, vp, sizeof(vp), cudaMemcpyHostToDevice, r->stream));
         TRYCU(cudaStreamSynchronize(r->stream));               // vp is a stack object
+    }
+
+    // ---- SVGF state (SVGFDenoiser::Init, src/kernels/svgf.cu:549-580) + the denoised image
+    if (cfg.denoiser) {
+        r->denoiser = true;
+        auto zeroed = [&](auto*& p, size_t count) -> int {
+            int rc = dev_alloc(r, p, count);
+            if (rc) return rc;
+            r->svgf_state.push_back({(void*)p, count * sizeof(*p)});
+            return PTB_OK;
+        };
+        for (int i = 0; i < 2; i++) { TRY(zeroed(r->svgf.direct[i], P)); TRY(zeroed(r->svgf.indirect[i], P)); TRY(zeroed(r->svgf.moments[i], P)); }
+        TRY(zeroed(r->svgf.history, P));
+        TRY(zeroed(r->svgf.prev_normal_matid, P));
+        TRY(zeroed(r->svgf.prev_depth, P));
+        TRY(zeroed(r->svgf.final_image, 3 * P));
+        for (auto& b : r->svgf_state) TRYCU(cudaMemsetAsync(b.first, 0, b.second, r->stream));
     }
 
     // ---- camera
@@ -464,7 +489,11 @@ int ptb_render_many(ptb_renderer* r, int32_t first, int32_t count) {
     CU(cudaSetDevice(r->device));
     for (int32_t it = first; it < first + count; it++) {
         // iteration 1 restarts the accumulation (src/pathtrace_wavefront.cu:232-242)
-        if (it == 1) r->kernel_launches += launch_clear_accumulators(r->frame, r->stream);
+        if (it == 1) {
+            r->kernel_launches += launch_clear_accumulators(r->frame, r->stream);
+            // WavefrontPathTracerState::clear() re-initialises the denoiser and the final image (src/wavefront_internal.cu:88-98)
+            for (auto& b : r->svgf_state) CU(cudaMemsetAsync(b.first, 0, b.second, r->stream));
+        }
         if (r->device_iteration != it) r->kernel_launches += launch_set_iteration(r->frame, it, r->stream);
         if (r->graph_exec) {
             CU(cudaGraphLaunch(r->graph_exec, r->stream));
@@ -491,14 +520,17 @@ int ptb_clear_accumulators(ptb_renderer* r) {
 
 int ptb_resolve(ptb_renderer* r, void* dst, int32_t format, int32_t iteration, int32_t dst_on_device) {
     if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_resolve: null argument");
-    if (format < PTB_IMG_SUM_RGB32F || format > PTB_IMG_VIEW_MOTION) return fail(PTB_ERR_INVALID, "ptb_resolve: unknown format");
-    const bool view = format >= PTB_IMG_VIEW_NORMALS;
+    if (format < PTB_IMG_SUM_RGB32F || format > PTB_IMG_DENOISED_RGBA8 || format == PTB_IMG_STEPS_I32) return fail(PTB_ERR_INVALID, "ptb_resolve: unknown format");
+    const bool den = format >= PTB_IMG_DENOISED_RGB32F;
+    if (den && !r->denoiser) return fail(PTB_ERR_STATE, "ptb_resolve: denoised output needs ptb_config.denoiser = 1");
+    const bool view = !den && format >= PTB_IMG_VIEW_NORMALS;
     if (view && !r->gbuffer) return fail(PTB_ERR_STATE, "ptb_resolve: G-buffer views need ptb_config.gbuffer = 1");
     if (!view && format != PTB_IMG_SUM_RGB32F && iteration < 1) return fail(PTB_ERR_INVALID, "ptb_resolve: iteration must be >= 1");
     CU(cudaSetDevice(r->device));
     const size_t P = (size_t)r->frame.num_paths;
-    const size_t bytes = P * ((format == PTB_IMG_RGBA8 || view) ? 4 : 12);
+    const size_t bytes = P * ((format == PTB_IMG_RGBA8 || format == PTB_IMG_DENOISED_RGBA8 || view) ? 4 : 12);
     auto run = [&](void* out) {
+        if (den) return launch_resolve_final(r->svgf.final_image, (int)P, out, format == PTB_IMG_DENOISED_RGBA8 ? PTB_IMG_RGBA8 : PTB_IMG_SUM_RGB32F, r->stream);
         if (view) return launch_view(r->gb, (int)P, out, format - PTB_IMG_VIEW_NORMALS + 1, r->stream);
         return launch_resolve(r->frame, out, format, iteration, r->stream);
     };

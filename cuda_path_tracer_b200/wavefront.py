@@ -107,12 +107,13 @@ class Scene:
 class Renderer:
     """An opaque ptb_renderer: PathtraceInit / Pathtrace / PathtraceFree on a handle."""
 
-    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False):
+    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False, denoiser=False):
         cfg = capi.Config()
         lib.ptb_config_default(C.byref(cfg))
         cfg.device, cfg.trace_depth, cfg.rank, cfg.world, cfg.stripe_rows = device, trace_depth, rank, world, stripe_rows
         cfg.use_graph = 1 if use_graph else 0
         cfg.gbuffer = 1 if gbuffer else 0
+        cfg.denoiser = 1 if denoiser else 0
         self._h = C.c_void_p()
         check(lib.ptb_init(scene._h, C.byref(cfg), C.byref(self._h)))
         t = capi.TileInfo()
@@ -133,7 +134,7 @@ class Renderer:
 
     def resolve(self, iteration, fmt=capi.IMG_MEAN_RGB32F, out=None):
         """(direct + indirect) / iteration for the owned pixels, into a host array."""
-        if fmt == capi.IMG_RGBA8 or fmt >= capi.IMG_VIEW_NORMALS:
+        if fmt in (capi.IMG_RGBA8, capi.IMG_DENOISED_RGBA8) or capi.IMG_VIEW_NORMALS <= fmt <= capi.IMG_VIEW_MOTION:
             out = np.empty((self.owned_pixels, 4), dtype=np.uint8) if out is None else out
         else:
             out = np.empty((self.owned_pixels, 3), dtype=np.float32) if out is None else out

@@ -144,7 +144,10 @@ typedef struct ptb_config {
     int32_t use_graph;       /* 1: replay the frame as a CUDA graph (default); 0: plain launches */
     int32_t gbuffer;         /* 1: keep the first-bounce G-buffer the reference's Logic writes every frame (depth, normal +
                                 material id, albedo, motion; src/kernels/logic.cu:66-73,119-138); 0 (default): skip it */
-    int32_t reserved[7];
+    int32_t denoiser;        /* 1: SVGF (src/kernels/svgf.cu) as in the reference's DenoiserOn mode: every frame is a fresh 1-spp
+                                estimate (accumulators cleared per frame, src/pathtrace_wavefront.cu:231-236), filtered into the
+                                final image; implies gbuffer; iteration 1 restarts the history; world must be 1 */
+    int32_t reserved[6];
 } ptb_config;
 void ptb_config_default(ptb_config* cfg);
 
@@ -182,7 +185,9 @@ int ptb_set_stream(ptb_renderer* r, void* cuda_stream);
  *                      (needs ptb_config.gbuffer): normals*0.5+0.5, 1-depth/500, albedo, motion*100+0.5 */
 enum { PTB_IMG_SUM_RGB32F = 0, PTB_IMG_MEAN_RGB32F = 1, PTB_IMG_RGBA8 = 2,
        PTB_IMG_VIEW_NORMALS = 3, PTB_IMG_VIEW_DEPTH = 4, PTB_IMG_VIEW_ALBEDO = 5, PTB_IMG_VIEW_MOTION = 6,
-       PTB_IMG_STEPS_I32 = 7 /* ptb_visualize_lbvh only: int32 node visits per pixel */ };
+       PTB_IMG_STEPS_I32 = 7 /* ptb_visualize_lbvh only: int32 node visits per pixel */,
+       PTB_IMG_DENOISED_RGB32F = 8 /* SVGF output d_final_image, float3, no gamma (needs ptb_config.denoiser) */,
+       PTB_IMG_DENOISED_RGBA8 = 9 /* the same through display mode 0: gamma 1/2.2, x255, clamp */ };
 int ptb_resolve(ptb_renderer* r, void* dst, int32_t format, int32_t iteration, int32_t dst_on_device);
 /* First-bounce G-buffer of the last rendered frame, one element per owned pixel (needs ptb_config.gbuffer):
  * WavefrontPathTracerState::d_depth / d_normal_matid / d_albedo / d_motion_vectors (src/wavefront_internal.cu:286-300). */

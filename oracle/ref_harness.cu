@@ -190,13 +190,14 @@ static double now_s() {
 int main(int argc, char** argv) {
     if (argc < 3) {
         fprintf(stderr,
-            "usage: refdump SCENE.json OUTDIR [--iters N] [--stages] [--selfcheck] [--bench K W] [--mega] [--no-dump] [--views]\n");
+            "usage: refdump SCENE.json OUTDIR [--iters N] [--stages] [--selfcheck] [--bench K W] [--mega] [--no-dump] [--views] [--denoise] [--denoise-bench K]\n");
         return 1;
     }
     std::string scene_file = argv[1];
     g_out = argv[2];
     int iters = 1, bench_k = 0, bench_w = 0;
-    bool stages = false, selfcheck = false, mega = false, no_dump = false, views = false;
+    bool stages = false, selfcheck = false, mega = false, no_dump = false, views = false, denoise = false;
+    int bench_d = 0;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         if (a == "--iters" && i + 1 < argc) iters = atoi(argv[++i]);
@@ -205,6 +206,8 @@ int main(int argc, char** argv) {
         else if (a == "--mega") mega = true;
         else if (a == "--no-dump") no_dump = true;
         else if (a == "--views") views = true;
+        else if (a == "--denoise") denoise = true;
+        else if (a == "--denoise-bench" && i + 1 < argc) { denoise = true; bench_d = atoi(argv[++i]); }
         else if (a == "--bench" && i + 2 < argc) { bench_k = atoi(argv[++i]); bench_w = atoi(argv[++i]); }
     }
     mkdir(g_out.c_str(), 0777);
@@ -255,6 +258,40 @@ int main(int argc, char** argv) {
                bench_k, dt * 1e3 / bench_k, bench_k * (double)P / dt / 1e6, mr / bench_k, t_init);
         pathtrace_wavefront::PathtraceFree();
         return 0;
+    }
+
+    if (denoise) {
+        // the reference's DenoiserOn mode through its untouched front-end: 1-spp frames + SVGF into d_final_image
+        gui.DenoiserOn = true;
+        for (int i = 1; i <= iters; i++) pathtrace_wavefront::Pathtrace(NULL, 0, i);
+        cudaDeviceSynchronize();
+        dump_dev("denoised", st->d_final_image, sizeof(glm::vec3) * P);
+        dump_dev("direct", st->d_direct_image, sizeof(glm::vec3) * P);
+        dump_dev("indirect", st->d_indirect_image, sizeof(glm::vec3) * P);
+        uchar4* pbo = nullptr;
+        cudaMalloc(&pbo, sizeof(uchar4) * P);
+        const dim3 bs(8, 8), grid((cam.resolution.x + 7) / 8, (cam.resolution.y + 7) / 8);
+        pathtrace_wavefront::SendImageToPBOKernel<<<grid, bs>>>(pbo, cam.resolution, iters, 0, true, st->d_final_image,
+            st->d_direct_image, st->d_indirect_image, st->d_normal_matid, st->d_depth, st->d_albedo, st->d_motion_vectors);
+        dump_dev("denoised_view0", pbo, sizeof(uchar4) * P);
+        cudaFree(pbo);
+        if (bench_d > 0) {   // filter cost alone: the reference's frame with and without the denoiser
+            double t[2];
+            for (int on = 0; on < 2; on++) {
+                gui.DenoiserOn = on != 0;
+                for (int i = 1; i <= 3; i++) pathtrace_wavefront::Pathtrace(NULL, 0, iters + i);
+                cudaDeviceSynchronize();
+                double t0 = now_s();
+                for (int i = 1; i <= bench_d; i++) pathtrace_wavefront::Pathtrace(NULL, 0, iters + 3 + i);
+                cudaDeviceSynchronize();
+                t[on] = (now_s() - t0) * 1e3 / bench_d;
+            }
+            printf("REFDENOISE {\"frames\": %d, \"ms_per_frame_plain\": %.4f, \"ms_per_frame_denoised\": %.4f, \"svgf_ms\": %.4f}\n", bench_d, t[0], t[1], t[1] - t[0]);
+        }
+        cudaError_t e = cudaGetLastError();
+        printf("REFDUMP {\"iters\": %d, \"pixels\": %d, \"cuda\": \"%s\"}\n", iters, P, cudaGetErrorString(e));
+        pathtrace_wavefront::PathtraceFree();
+        return e == cudaSuccess ? 0 : 4;
     }
 
     if (selfcheck) {

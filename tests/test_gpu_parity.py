@@ -319,3 +319,35 @@ def test_gbuffer_views_and_heatmap_vs_reference(which, iters, sponza_small, tmp_
         plain.gbuffer("depth")
     assert e.value.code == capi.ERR_STATE
     plain.free()
+
+
+# ------------------------------------------------------------------------------------------ SVGF denoiser
+@pytest.mark.parametrize("which,iters", [("cornell", 1), ("cornell", 6), ("sponza_small", 3), ("sponza_small", 8)])
+def test_svgf_vs_reference(which, iters, sponza_small, tmp_path):
+    """The reference's DenoiserOn mode through its untouched Pathtrace(): 1-spp frames, SVGF (temporal accumulation with
+    history, spatial variance, 5 a-trous levels, modulation) into d_final_image.  Bit-exact, including frames where the
+    temporal variance takes over from the spatial estimate (history >= 4)."""
+    _need_ref()
+    scene_json = scenegen.cornell(str(tmp_path / "c"), res=(200, 160)) if which == "cornell" else sponza_small
+    d = str(tmp_path / "ref")
+    par.run_refdump(scene_json, d, iters=iters, stages=False, denoise=True)
+    ref = par.RefDump(d)
+    r = ptb.Renderer(ptb.Scene(scene_json), denoiser=True)
+    r.render(1, iters)
+    dn, inn = r.accumulators()            # the last frame's 1-spp estimate: the accumulators are cleared every frame
+    assert _bits(dn, ref.load("direct", "<f4", 3)) and _bits(inn, ref.load("indirect", "<f4", 3))
+    assert _bits(r.resolve(iters, capi.IMG_DENOISED_RGB32F), ref.load("denoised", "<f4", 3))
+    assert np.array_equal(r.resolve(iters, capi.IMG_DENOISED_RGBA8), ref.load("denoised_view0", "u1", 4))
+    # iteration 1 restarts the history: rendering the same frames again gives the same image
+    first = r.resolve(iters, capi.IMG_DENOISED_RGB32F)
+    r.render(1, iters)
+    assert _bits(r.resolve(iters, capi.IMG_DENOISED_RGB32F), first)
+    r.free()
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Renderer(ptb.Scene(scene_json), denoiser=True, rank=0, world=2)
+    assert e.value.code == capi.ERR_UNSUPPORTED
+    plain = ptb.Renderer(ptb.Scene(scene_json))
+    with pytest.raises(capi.PtbError) as e:
+        plain.resolve(1, capi.IMG_DENOISED_RGB32F)
+    assert e.value.code == capi.ERR_STATE
+    plain.free()
