@@ -21,13 +21,15 @@ struct GBufferDev {                      // first-bounce G-buffer, one entry per
 };
 
 struct SvgfDev {                         // SVGFDenoiser's owned buffers (src/kernels/svgf.h:55-72), 120 B per pixel + the output
-    float4* direct[2];                   // demodulated direct light (rgb) + variance (w), ping-pong
+    float4* direct[2];                   // demodulated direct light (rgb) + variance (w): [0] work, [1] history
     float4* indirect[2];
     float4* moments[2];                  // (lum_dir, lum_ind, lum_dir^2, lum_ind^2)
     int* history;                        // frames of valid history per pixel
     float4* prev_normal_matid;           // last frame's G-buffer for the consistency test
     float* prev_depth;
     float* final_image;                  // float3: (direct + indirect) * albedo, no gamma (d_final_image)
+    int* short_list;                     // pixels with fewer than 4 frames of history (they get the spatial variance estimate)
+    int* short_count;
 };
 
 struct FrameDev {
@@ -82,7 +84,7 @@ int launch_gbuffer(const FrameDev& f, const GBufferDev& g, cudaStream_t s);
 int launch_view(const GBufferDev& g, int n, void* dst_rgba8, int mode, cudaStream_t s);   // SendImageToPBOKernel modes 1-4
 int launch_bvh_heatmap(const FrameDev& f, float* out_rgb, int* out_steps, cudaStream_t s);
 // SVGF (svgf.cu): one frame of the filter over the 1-spp accumulators, 8 kernels
-int launch_svgf(const FrameDev& f, const SvgfDev& s, const GBufferDev& g, cudaStream_t st);
+int launch_svgf(const FrameDev& f, const SvgfDev& s, const GBufferDev& g, int num_sms, cudaStream_t st);
 int launch_resolve_final(const float* final_image, int n, void* dst, int format, cudaStream_t s);
 
 // Batched RayCast on caller rays (ptb_trace_closest / ptb_trace_occluded): device arrays.

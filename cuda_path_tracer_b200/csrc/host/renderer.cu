@@ -198,7 +198,7 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
         if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
     }
-    if (r->denoiser) n += launch_svgf(f, r->svgf, r->gb, s);   // reads *f.iteration: before frame_end advances it
+    if (r->denoiser) n += launch_svgf(f, r->svgf, r->gb, r->launch.num_sms, s);   // reads *f.iteration: before frame_end advances it
     n += launch_frame_end(f, r->launch, s);
     return n;
 }
@@ -430,6 +430,8 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         TRY(zeroed(r->svgf.prev_normal_matid, P));
         TRY(zeroed(r->svgf.prev_depth, P));
         TRY(zeroed(r->svgf.final_image, 3 * P));
+        TRY(zeroed(r->svgf.short_list, P));
+        TRY(zeroed(r->svgf.short_count, 1));
         for (auto& b : r->svgf_state) TRYCU(cudaMemsetAsync(b.first, 0, b.second, r->stream));
     }
 
