@@ -15,6 +15,7 @@
 
 #include "json_mini.hpp"
 #include "obj_loader.hpp"
+#include "parallel.hpp"
 
 namespace ptb {
 
@@ -245,10 +246,116 @@ static ptb_material material_from_mtl(ptb_scene& s, const MtlMaterial& t, const 
     return m;
 }
 
+// ---- order-preserving parallel de-duplication ---------------------------------------------------------------------
+// The reference numbers vertices by first occurrence while it walks the corners in file order through one
+// unordered_map (src/scene.cpp:330-539) -- 30 M dependent hash probes at 10 M triangles.  The numbering only depends
+// on, per corner, the earliest corner with an equal key.  Corners are bucketed by hash into shards (stable, so every
+// shard still sees its corners in file order), each shard finds first occurrences in its own small table, and an
+// exclusive scan over the "is a first occurrence" flags in corner order gives exactly the sequential ids.
+namespace {
+
+struct CornerStage {
+    std::vector<VKey> key;          // 3 per triangle
+    std::vector<uint64_t> hash;
+    std::vector<V3> tangent;        // per triangle
+    std::vector<int32_t> material;  // per triangle
+};
+
+void dedup_and_emit(CornerStage& st, ptb_scene& s, int threads) {
+    const size_t C = st.key.size();
+    const size_t T = C / 3;
+    if (C == 0) return;
+    if (C >= 0x7fffffffull) throw std::runtime_error("scene too large: more than 2^31 triangle corners");
+    size_t S = 1;
+    while (S < (size_t)threads * 2 && S < 256) S <<= 1;
+    auto shard_of = [S](uint64_t h) { return (size_t)(h >> 40) & (S - 1); };
+
+    // stable bucketing of corner indices by shard
+    size_t R = std::max<size_t>(1, std::min<size_t>((size_t)threads, (C + 65535) / 65536));
+    std::vector<size_t> count(R * S, 0);
+    parallel_tasks(R, threads, [&](size_t r) {
+        size_t* cnt = &count[r * S];
+        for (size_t c = C * r / R; c < C * (r + 1) / R; c++) cnt[shard_of(st.hash[c])]++;
+    });
+    std::vector<size_t> shard_begin(S + 1, 0);
+    {
+        size_t run = 0;
+        for (size_t sh = 0; sh < S; sh++) {
+            shard_begin[sh] = run;
+            for (size_t r = 0; r < R; r++) { size_t n = count[r * S + sh]; count[r * S + sh] = run; run += n; }
+        }
+        shard_begin[S] = run;
+    }
+    std::vector<uint32_t> order(C);
+    parallel_tasks(R, threads, [&](size_t r) {
+        size_t* pos = &count[r * S];
+        for (size_t c = C * r / R; c < C * (r + 1) / R; c++) order[pos[shard_of(st.hash[c])]++] = (uint32_t)c;
+    });
+
+    // first occurrence per corner
+    std::vector<uint32_t> first(C);
+    VKeyEq eq;
+    parallel_tasks(S, threads, [&](size_t sh) {
+        const size_t n = shard_begin[sh + 1] - shard_begin[sh];
+        if (n == 0) return;
+        size_t cap = 16;
+        while (cap < n * 2) cap <<= 1;
+        std::vector<uint32_t> table(cap, 0xffffffffu);
+        for (size_t k = shard_begin[sh]; k < shard_begin[sh + 1]; k++) {
+            const uint32_t c = order[k];
+            size_t slot = (size_t)st.hash[c] & (cap - 1);
+            for (;;) {
+                uint32_t o = table[slot];
+                if (o == 0xffffffffu) { table[slot] = c; first[c] = c; break; }
+                if (st.hash[o] == st.hash[c] && eq(st.key[o], st.key[c])) { first[c] = o; break; }
+                slot = (slot + 1) & (cap - 1);
+            }
+        }
+    });
+
+    // ids = exclusive scan of the first-occurrence flags in corner order
+    std::vector<uint32_t> id(C);
+    std::vector<size_t> part(R + 1, 0);
+    parallel_tasks(R, threads, [&](size_t r) {
+        size_t n = 0;
+        for (size_t c = C * r / R; c < C * (r + 1) / R; c++) n += (first[c] == c);
+        part[r + 1] = n;
+    });
+    for (size_t r = 0; r < R; r++) part[r + 1] += part[r];
+    const size_t base = s.pos.size();
+    const size_t V = part[R];
+    s.pos.resize(base + V);
+    s.raw_nor.resize(base + V);
+    s.raw_tangent.resize(base + V);
+    s.uv.resize(base + V);
+    parallel_tasks(R, threads, [&](size_t r) {
+        size_t next = base + part[r];
+        for (size_t c = C * r / R; c < C * (r + 1) / R; c++) {
+            if (first[c] != c) continue;
+            const float* k = st.key[c].v;
+            id[c] = (uint32_t)next;
+            s.pos[next] = f4{k[0], k[1], k[2], 1.0f};
+            s.raw_nor[next] = V3(k[3], k[4], k[5]);
+            s.raw_tangent[next] = st.tangent[c / 3];   // the tangent of the triangle that introduced the vertex
+            s.uv[next] = f2{k[6], k[7]};
+            next++;
+        }
+    });
+    const size_t tri_base = s.indices_matid.size();
+    s.indices_matid.resize(tri_base + T);
+    parallel_ranges(T, threads, [&](size_t b, size_t e) {
+        for (size_t t = b; t < e; t++)
+            s.indices_matid[tri_base + t] = i4{(int32_t)id[first[3 * t]], (int32_t)id[first[3 * t + 1]], (int32_t)id[first[3 * t + 2]], st.material[t]};
+    });
+}
+
+}  // namespace
+
 static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unordered_map<std::string, uint32_t>& name_to_id) {
     // src/scene.cpp:330-539
-    std::unordered_map<VKey, int32_t, VKeyHash, VKeyEq> unique;
-    unique.reserve(100000);
+    const int threads = loader_threads();
+    CornerStage st;
+    VKeyHash hasher;
     for (const JsonValue& p : objects.arr) {
         bool forced = false;
         int forced_id = -1;
@@ -292,62 +399,64 @@ static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unor
             d.roughness = 0.5f; d.metallic = 0.0f; d.type = 0;
             s.materials.push_back(d);
         }
+        // per-triangle work has no order dependence: transform, tangent, geometric normal, corner keys
         const size_t ntri = obj.tri_material.size();
-        for (size_t f = 0; f < ntri; f++) {
-            V3 vpos[3], vnor[3];
-            V2 vuv[3];
-            for (int i = 0; i < 3; i++) {
-                const ObjIndex& ix = obj.tri_indices[f * 3 + i];
-                V4 rp(obj.v[3 * ix.v + 0], obj.v[3 * ix.v + 1], obj.v[3 * ix.v + 2], 1.0f);
-                V4 tp = transform * rp;
-                vpos[i] = V3(tp.x, tp.y, tp.z);
-                if (ix.vt >= 0) { vuv[i].x = obj.vt[2 * ix.vt + 0]; vuv[i].y = 1.0f - obj.vt[2 * ix.vt + 1]; }
-                if (ix.vn >= 0) {
-                    V4 rn(obj.vn[3 * ix.vn + 0], obj.vn[3 * ix.vn + 1], obj.vn[3 * ix.vn + 2], 0.0f);
-                    V4 tn = inv_t * rn;
-                    vnor[i] = normalize(V3(tn.x, tn.y, tn.z));
+        const size_t t0 = st.tangent.size();
+        st.key.resize((t0 + ntri) * 3);
+        st.hash.resize((t0 + ntri) * 3);
+        st.tangent.resize(t0 + ntri);
+        st.material.resize(t0 + ntri);
+        const size_t g0 = s.nor_geom.size();
+        s.nor_geom.resize(g0 + ntri);
+        parallel_ranges(ntri, threads, [&](size_t fb, size_t fe) {
+            for (size_t f = fb; f < fe; f++) {
+                V3 vpos[3], vnor[3];
+                V2 vuv[3];
+                for (int i = 0; i < 3; i++) {
+                    const ObjIndex& ix = obj.tri_indices[f * 3 + i];
+                    V4 rp(obj.v[3 * ix.v + 0], obj.v[3 * ix.v + 1], obj.v[3 * ix.v + 2], 1.0f);
+                    V4 tp = transform * rp;
+                    vpos[i] = V3(tp.x, tp.y, tp.z);
+                    if (ix.vt >= 0) { vuv[i].x = obj.vt[2 * ix.vt + 0]; vuv[i].y = 1.0f - obj.vt[2 * ix.vt + 1]; }
+                    if (ix.vn >= 0) {
+                        V4 rn(obj.vn[3 * ix.vn + 0], obj.vn[3 * ix.vn + 1], obj.vn[3 * ix.vn + 2], 0.0f);
+                        V4 tn = inv_t * rn;
+                        vnor[i] = normalize(V3(tn.x, tn.y, tn.z));
+                    }
+                }
+                V3 e1 = vpos[1] - vpos[0], e2 = vpos[2] - vpos[0];
+                float du1x = vuv[1].x - vuv[0].x, du1y = vuv[1].y - vuv[0].y;
+                float du2x = vuv[2].x - vuv[0].x, du2y = vuv[2].y - vuv[0].y;
+                float det = du1x * du2y - du2x * du1y;
+                V3 tangent(0, 0, 0);
+                if (std::abs(det) > 1e-6f) {
+                    float inv_det = 1.0f / det;
+                    tangent = inv_det * (du2y * e1 - du1y * e2);
+                }
+                V3 ng = normalize(cross(e1, e2));
+                s.nor_geom[g0 + f] = f4{ng.x, ng.y, ng.z, 0.0f};
+                st.tangent[t0 + f] = tangent;
+                st.material[t0 + f] = forced ? forced_id : (mat_start + std::max(0, obj.tri_material[f]));
+                for (int i = 0; i < 3; i++) {
+                    VKey k = {{vpos[i].x, vpos[i].y, vpos[i].z, vnor[i].x, vnor[i].y, vnor[i].z, vuv[i].x, vuv[i].y}};
+                    st.key[(t0 + f) * 3 + i] = k;
+                    st.hash[(t0 + f) * 3 + i] = (uint64_t)hasher(k);
                 }
             }
-            V3 e1 = vpos[1] - vpos[0], e2 = vpos[2] - vpos[0];
-            float du1x = vuv[1].x - vuv[0].x, du1y = vuv[1].y - vuv[0].y;
-            float du2x = vuv[2].x - vuv[0].x, du2y = vuv[2].y - vuv[0].y;
-            float det = du1x * du2y - du2x * du1y;
-            V3 tangent(0, 0, 0);
-            if (std::abs(det) > 1e-6f) {
-                float inv_det = 1.0f / det;
-                tangent = inv_det * (du2y * e1 - du1y * e2);
-            }
-            V3 ng = normalize(cross(e1, e2));
-            s.nor_geom.push_back(f4{ng.x, ng.y, ng.z, 0.0f});
-            int mat = forced ? forced_id : (mat_start + std::max(0, obj.tri_material[f]));
-            int32_t vid[3];
-            for (int i = 0; i < 3; i++) {
-                VKey k = {{vpos[i].x, vpos[i].y, vpos[i].z, vnor[i].x, vnor[i].y, vnor[i].z, vuv[i].x, vuv[i].y}};
-                auto it = unique.find(k);
-                if (it == unique.end()) {
-                    int32_t id = (int32_t)s.pos.size();
-                    unique.emplace(k, id);
-                    s.pos.push_back(f4{vpos[i].x, vpos[i].y, vpos[i].z, 1.0f});
-                    s.raw_nor.push_back(vnor[i]);
-                    s.raw_tangent.push_back(tangent);
-                    s.uv.push_back(f2{vuv[i].x, vuv[i].y});
-                    vid[i] = id;
-                } else {
-                    vid[i] = it->second;
-                }
-            }
-            s.indices_matid.push_back(i4{vid[0], vid[1], vid[2], mat});
-        }
+        });
     }
+    dedup_and_emit(st, s, threads);
     // upload-time normalisation (src/wavefront_internal.cu:136-144): zero vectors become NaN, as there
     s.nor.resize(s.pos.size());
     s.tangent.resize(s.pos.size());
-    for (size_t i = 0; i < s.pos.size(); i++) {
-        V3 n = normalize(s.raw_nor[i]);
-        V3 t = normalize(s.raw_tangent[i]);
-        s.nor[i] = f4{n.x, n.y, n.z, 0.0f};
-        s.tangent[i] = f4{t.x, t.y, t.z, 0.0f};
-    }
+    parallel_ranges(s.pos.size(), threads, [&](size_t b, size_t e) {
+        for (size_t i = b; i < e; i++) {
+            V3 n = normalize(s.raw_nor[i]);
+            V3 t = normalize(s.raw_tangent[i]);
+            s.nor[i] = f4{n.x, n.y, n.z, 0.0f};
+            s.tangent[i] = f4{t.x, t.y, t.z, 0.0f};
+        }
+    });
 }
 
 void load_scene_json(const std::string& path, ptb_scene& s) {

@@ -48,6 +48,16 @@ class Scene:
             check(lib.ptb_scene_load(str(filename).encode(), C.byref(self._h)))
 
     @classmethod
+    def load_cache(cls, filename):
+        """A scene written by save_cache(): no parsing, no de-duplication, bit-identical arrays."""
+        h = C.c_void_p()
+        check(lib.ptb_scene_load_cache(str(filename).encode(), C.byref(h)))
+        return cls(_handle=h)
+
+    def save_cache(self, filename):
+        check(lib.ptb_scene_save_cache(self._h, str(filename).encode()))
+
+    @classmethod
     def from_arrays(cls, pos, nor, indices, material_ids, materials, camera, uv=None, tangent=None, trace_depth=8):
         """camera: dict(resolution=(w,h), fovy=deg, eye=, look_at=, up=)."""
         pos = np.ascontiguousarray(pos, dtype=np.float32).reshape(-1, 3)

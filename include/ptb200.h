@@ -94,6 +94,13 @@ int ptb_scene_set_environment(ptb_scene* s, const float* rgb, int32_t width, int
  * (src/scene.cpp:560-572) and store it in the scene. */
 int ptb_scene_set_camera(ptb_scene* s, const int32_t resolution[2], float fovy_deg,
                          const float eye[3], const float look_at[3], const float up[3], int32_t trace_depth);
+/* Binary scene cache: the loaded scene (geometry in upload layout, materials, light CDF, decoded textures, the
+ * environment alias table, camera) written verbatim, so a later start skips OBJ / MTL / image parsing,
+ * de-duplication and table building (Scene::Scene does all of that on every run, src/scene.cpp:45-631).
+ * A scene read back is bit-identical to the one saved.  Host byte order; PTB_ERR_PARSE for a file that is not a
+ * cache of this version, is truncated or fails the index range checks. */
+int ptb_scene_save_cache(const ptb_scene* s, const char* path);
+int ptb_scene_load_cache(const char* path, ptb_scene** out);
 void ptb_scene_free(ptb_scene* s);
 
 /* Image::savePNG / Image::saveHDR (src/image.cpp:22-49) with the transform of main.cpp's saveImage()

@@ -198,6 +198,7 @@ int main(int argc, char** argv) {
     int iters = 1, bench_k = 0, bench_w = 0;
     bool stages = false, selfcheck = false, mega = false, no_dump = false, views = false, denoise = false;
     int bench_d = 0;
+    bool load_only = false;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         if (a == "--iters" && i + 1 < argc) iters = atoi(argv[++i]);
@@ -207,6 +208,7 @@ int main(int argc, char** argv) {
         else if (a == "--no-dump") no_dump = true;
         else if (a == "--views") views = true;
         else if (a == "--denoise") denoise = true;
+        else if (a == "--load-only") load_only = true;   // time the reference's scene loader (host only) and stop
         else if (a == "--denoise-bench" && i + 1 < argc) { denoise = true; bench_d = atoi(argv[++i]); }
         else if (a == "--bench" && i + 2 < argc) { bench_k = atoi(argv[++i]); bench_w = atoi(argv[++i]); }
     }
@@ -214,7 +216,24 @@ int main(int argc, char** argv) {
     cudaSetDevice(0);
     cudaFree(0);
 
+    double t_load0 = now_s();
     Scene* scene = new Scene(scene_file);
+    double t_load = now_s() - t_load0;
+    if (load_only) {
+        // position-weighted word sum (vectorisable on the checking side) over what the de-duplication decides:
+        // vertex positions and uvs in id order, then the index triples, then the material ids
+        unsigned long long h = 0, n = 0;
+        auto mix = [&](const void* p, size_t words) {
+            const unsigned int* w = (const unsigned int*)p;
+            for (size_t i = 0; i < words; i++, n++) h += ((unsigned long long)w[i] + 1ull) * (n * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull);
+        };
+        for (const Vertex& v : scene->vertices) { mix(&v.pos, 3); mix(&v.uv, 2); }
+        mix(scene->indices.data(), scene->indices.size());
+        mix(scene->materialIds.data(), scene->materialIds.size());
+        printf("REFLOAD {\"load_s\": %.4f, \"triangles\": %zu, \"vertices\": %zu, \"checksum\": \"%016llx\"}\n", t_load, scene->indices.size() / 3,
+               scene->vertices.size(), h);
+        return 0;
+    }
     const Camera& cam = scene->state.camera;
     const int P = cam.resolution.x * cam.resolution.y;
 

@@ -55,6 +55,123 @@ def test_loader_matches_reference_upload(golden, tmp_path, case, gen):
     assert (i.num_triangles, i.num_vertices, i.width, i.height, i.trace_depth, i.num_materials, i.num_lights) == (n, v, w, h, depth, nmat, nl)
 
 
+@pytest.mark.parametrize("threads,chunk", [("1", None), ("4", "64"), ("3", "1000")])
+def test_parallel_loader_matches_reference_upload(golden, tmp_path, monkeypatch, threads, chunk):
+    """The chunked OBJ parse and the sharded de-duplication give the reference's arrays for any thread / chunk count."""
+    monkeypatch.setenv("PTB_LOADER_THREADS", threads)
+    if chunk: monkeypatch.setenv("PTB_LOADER_CHUNK_BYTES", chunk)
+    g = golden("fire_tiny")
+    s = ptb.Scene(scenegen.fireplace(str(tmp_path / "f"), res=(96, 54), scale=0.1)[0])
+    for name, key in (("pos", "mesh_pos"), ("nor", "mesh_nor"), ("uv", "mesh_uv"), ("indices_matid", "mesh_indices_matid"),
+                      ("nor_geom", "mesh_nor_geom"), ("light_tri_idx", "light_tri_idx"), ("light_cdf", "light_cdf")):
+        assert _bits(s.array(name), g[key]), name
+
+
+OBJ_ODDITIES = """# relative indices, quads, groups, material switches, CRLF and bare CR line ends, a forward reference
+mtllib odd.mtl
+v 0 0 0
+v 1 0 0
+v 1 1 0
+v 0 1 0.25
+vn 0 0 1
+vt 0 0
+vt 1 0
+vt 1 1
+vt 0 1
+usemtl red
+f 1/1/1 2/2/1 3/3/1 4/4/1
+f -4//-1 -3//-1 -2//-1
+g second
+v 2 0 0
+v 2 1 0
+usemtl blue
+f 2/2 5/1 6/4 3/3
+usemtl blue
+f -1 -2 -5
+f 1 2 7 8
+o third
+v 3 0 0
+v 3 1 0
+usemtl nosuch
+f 5 7 8 6
+f 1 2
+"""
+
+
+def _write_oddities(d):
+    os.makedirs(d, exist_ok=True)
+    open(os.path.join(d, "odd.obj"), "w", newline="").write(OBJ_ODDITIES)
+    open(os.path.join(d, "odd.mtl"), "w").write("newmtl red\nKd 1 0 0\nnewmtl blue\nKd 0 0 1\n")
+    cam = {"RES": [8, 8], "FOVY": 45.0, "ITERATIONS": 1, "DEPTH": 2, "FILE": "odd", "EYE": [0.0, 0.0, 5.0], "LOOKAT": [0.0, 0.0, 0.0], "UP": [0.0, 1.0, 0.0]}
+    path = os.path.join(d, "scene.json")
+    scenegen.write_scene(path, cam, {"grey": scenegen._mat([0.5, 0.5, 0.5])}, [scenegen._obj_entry(os.path.join(d, "odd.obj"))])
+    return path
+
+
+def test_chunked_obj_parse_equals_single_pass(tmp_path, monkeypatch):
+    """Every chunk size cuts the statement stream at different places; the triangles, their order, their materials
+    and the de-duplicated vertices must not depend on it.  The quad `f 1 2 7 8` names vertices that are defined only
+    after the flush that exports it (tinyobj drops it); the 2-corner face is dropped as degenerate."""
+    path = _write_oddities(str(tmp_path / "odd"))
+    ref = None
+    for threads, chunk in (("1", "100000000"), ("1", "1"), ("2", "16"), ("8", "40"), ("5", "97")):
+        monkeypatch.setenv("PTB_LOADER_THREADS", threads)
+        monkeypatch.setenv("PTB_LOADER_CHUNK_BYTES", chunk)
+        s = ptb.Scene(path)
+        got = {k: s.array(k) for k in ("pos", "nor", "uv", "tangent", "indices_matid", "nor_geom")}
+        if ref is None:
+            ref = got
+            im = got["indices_matid"]
+            assert im.shape[0] == 2 + 1 + 2 + 1 + 2          # quad, tri, quad, tri, (dropped quad), quad; degenerate dropped
+            # JSON material 0, then the MTL's red = 1, blue = 2; "nosuch" is tinyobj id -1, which the loader clamps to its first
+            assert list(im[:, 3]) == [1, 1, 1, 2, 2, 2, 1, 1]
+            refdump = os.path.join(ROOT, "oracle", "_ref", "refdump")
+            if os.path.exists(refdump):   # the reference's own loader on the same file (host-only mode of the harness)
+                import json, subprocess
+                sys_path = os.path.join(ROOT, "tools")
+                q = subprocess.run([refdump, path, str(tmp_path / "ref"), "--load-only"], capture_output=True, text=True)
+                line = [l for l in q.stdout.splitlines() if l.startswith("REFLOAD")]
+                assert line, q.stdout + q.stderr
+                r = json.loads(line[0][8:])
+                import importlib.util
+                spec = importlib.util.spec_from_file_location("measure_ingest", os.path.join(sys_path, "measure_ingest.py"))
+                mi = importlib.util.module_from_spec(spec); spec.loader.exec_module(mi)
+                assert (r["triangles"], r["vertices"]) == (im.shape[0], got["pos"].shape[0])
+                assert r["checksum"] == mi.checksum(s)
+        else:
+            for k in ref:
+                assert _bits(ref[k], got[k]), (k, threads, chunk)
+        s.free()
+
+
+def test_scene_cache_roundtrip(tmp_path):
+    """ptb_scene_save_cache / ptb_scene_load_cache: every array, the info block and the camera come back bit for bit;
+    damaged files are PTB_ERR_PARSE, not crashes."""
+    path = scenegen.sponza(str(tmp_path / "sp"), res=(64, 36), scale=0.05, tex_size=32)[0]
+    s = ptb.Scene(path)
+    cache = str(tmp_path / "scene.ptbscene")
+    s.save_cache(cache)
+    c = ptb.Scene.load_cache(cache)
+    from cuda_path_tracer_b200.wavefront import SA
+    for name in SA:
+        assert _bits(s.array(name), c.array(name)), name
+    for f, _ in capi.SceneInfo._fields_:
+        a, b = getattr(s.info, f), getattr(c.info, f)
+        assert (list(a) == list(b)) if hasattr(a, "__len__") else (a == b), f
+    assert bytes(s.camera) == bytes(c.camera)
+    assert c.info.num_textures > 0 and c.info.env_tex_id >= 0
+    blob = open(cache, "rb").read()
+    for bad in (blob[: len(blob) // 2], b"NOTACACHE" + blob[9:], blob + b"x", blob[:8] + b"\x09\x00\x00\x00" + blob[12:]):
+        p = str(tmp_path / "bad.ptbscene")
+        open(p, "wb").write(bad)
+        with pytest.raises(capi.PtbError) as e:
+            ptb.Scene.load_cache(p)
+        assert e.value.code == capi.ERR_PARSE
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Scene.load_cache(str(tmp_path / "missing.ptbscene"))
+    assert e.value.code == capi.ERR_IO
+
+
 def test_material_ids_follow_sorted_json_keys(tmp_path):
     s = ptb.Scene(scenegen.cornell(str(tmp_path / "c"), res=(8, 8)))
     m = s.array("materials")
