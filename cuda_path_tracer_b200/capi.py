@@ -55,7 +55,7 @@ class SceneInfo(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("trace_depth", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("denoiser", C.c_int32), ("reserved", C.c_int32 * 6)]
+                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("denoiser", C.c_int32), ("env_nee", C.c_int32), ("reserved", C.c_int32 * 5)]
 
 
 class TileInfo(C.Structure):
@@ -93,6 +93,7 @@ SIGNATURES = {
     "ptb_save_image": (C.c_int, [C.c_char_p, P, C.c_int32, C.c_int32, C.c_float, C.c_int32]),
     "ptb_get_gbuffer": (C.c_int, [P, C.c_int32, P, C.c_size_t]),
     "ptb_visualize_lbvh": (C.c_int, [P, P, C.c_int32, C.c_int32]),
+    "ptb_sample_environment": (C.c_int, [P, P, C.c_int32, P, P, P]),
     "ptb_sync": (C.c_int, [P]),
     "ptb_set_stream": (C.c_int, [P, P]),
     "ptb_resolve": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32]),

@@ -3,6 +3,7 @@
 // and the stage wrappers of src/kernels/{ray_gen,ray_cast,logic,shading}.h.
 #pragma once
 #include "common.cuh"
+#include "envmap.cuh"
 
 namespace ptb {
 
@@ -53,6 +54,7 @@ struct FrameDev {
     TileMap tile;
     int trace_depth;
     int num_paths;            // == tile.owned_pixels
+    EnvDev env;               // alias table of the HDR environment + ptb_config.env_nee
 };
 
 struct LaunchCfg {
@@ -77,6 +79,8 @@ int launch_trace_shadow(const FrameDev& f, int bounce, const LaunchCfg& c, cudaS
 int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s);
 int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
 int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
+int launch_fold_env(const FrameDev& f, cudaStream_t s);
+int launch_sample_environment(const FrameDev& f, const float* rnd, int n, float* dir, float* pdf, int* pixel, cudaStream_t s);
 int launch_frame_end(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);                   // ray statistics
 int launch_resolve(const FrameDev& f, void* dst, int format, int iteration, cudaStream_t s);
 // headless views (views.cu)

@@ -108,9 +108,12 @@ struct ShadeOut {
     bool push_ext;
     bool push_shadow;
     float4 sh_ori_tmax, sh_dir, sh_rad;
+    bool push_env;                         // ENV only: the environment's next-event ray
+    float4 env_dir, env_rad;               // (its origin is the light ray's: P + Ng * eps)
+    float4 env_ori_tmax;
 };
 
-template <int TYPE>
+template <int TYPE, bool ENV>
 __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut& out) {
     float4 dd = f.pool.ray_dir_dist[idx];
     float4 oo = f.pool.ray_ori[idx];
@@ -175,6 +178,34 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
         }
     }
 
+    // ---- the environment's next-event estimate (ptb_config.env_nee; see envmap.cuh).  Its random numbers come from
+    // a stream hashed off the path's state, which is not advanced: the BSDF sample below, hence the whole path and
+    // the indirect image, are the same with the flag on or off, and the light's estimate above is untouched.
+    if (ENV && (TYPE == MAT_PBR || TYPE == MAT_DIFFUSE)) {
+        uint32_t env_seed = wang_hash(seed ^ 0x85ebca6bu);
+        if (env_seed == 0) env_seed = 1;
+        float r0 = rand_float(env_seed), r1 = rand_float(env_seed);
+        float pdf_env, eu, ev; int texel;
+        Vec3 wi = sample_environment(f.env, f.tex, r0, r1, pdf_env, texel, eu, ev);
+        float cos_surf = fmaxf(dot3(N, wi), 0.0f);
+        if (dot3(Ng, wi) > 0.0f && cos_surf > 0.0f && pdf_env > 0.0f) {
+            Vec3 fr = eval_bsdf(wo, wi, N, m);
+            float pdf = pdf_bsdf(wo, wi, N, m);
+            if (length3(fr) > 0.0f && !(pdf > PTB_PDF_DIRAC_DELTA)) {
+                float4 e4 = tex2D<float4>(__ldg(&f.tex.handles[f.tex.env_tex_id]), eu, ev);
+                // the complement of Logic's weight for the BSDF-sampled hit of the same direction (logic.cuh, src/kernels/logic.cu:99)
+                float weight = (pdf_env * pdf_env + PTB_EPSILON) / (pdf * pdf + pdf_env * pdf_env + PTB_EPSILON);
+                Vec3 L = throughput * Vec3(e4.x, e4.y, e4.z) * fr * (cos_surf * weight / pdf_env);
+                if (length3(L) > 0.0f) {
+                    out.push_env = true;
+                    out.env_ori_tmax = make_float4(P.x + Ng.x * PTB_EPSILON, P.y + Ng.y * PTB_EPSILON, P.z + Ng.z * PTB_EPSILON, FLT_MAX);
+                    out.env_dir = make_float4(wi.x, wi.y, wi.z, 0.0f);
+                    out.env_rad = make_float4(L.x, L.y, L.z, 0.0f);
+                }
+            }
+        }
+    }
+
     Vec3 next_dir(0.0f);
     float next_pdf = 0.0f;
     Vec3 att;
@@ -214,7 +245,7 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
 #ifndef PTB_SHADE_MINBLOCKS
 #define PTB_SHADE_MINBLOCKS 1
 #endif
-template <int TYPE>
+template <int TYPE, bool ENV>
 __global__ void __launch_bounds__(kThreads, PTB_SHADE_MINBLOCKS) k_shade(const __grid_constant__ FrameDev f, int bounce) {
     const int* ctr = f.ctr + bounce * CTR_STRIDE;
     int* next = f.ctr + (bounce + 1) * CTR_STRIDE;
@@ -226,10 +257,11 @@ __global__ void __launch_bounds__(kThreads, PTB_SHADE_MINBLOCKS) k_shade(const _
         ShadeOut out;
         out.push_ext = false;
         out.push_shadow = false;
+        out.push_env = false;
         int idx = -1;
         if (i < n) {
             idx = __ldg(&f.q_mat[TYPE][i]);
-            shade_path<TYPE>(f, idx, out);
+            shade_path<TYPE, ENV>(f, idx, out);
         }
         int sp = warp_append(out.push_shadow, &next[CTR_SHADOW]);
         if (sp >= 0) {
@@ -237,6 +269,15 @@ __global__ void __launch_bounds__(kThreads, PTB_SHADE_MINBLOCKS) k_shade(const _
             f.shadow.ray_dir[sp] = out.sh_dir;
             f.shadow.radiance[sp] = out.sh_rad;
             f.shadow.slot[sp] = idx;
+        }
+        if (ENV) {   // second shadow-queue entry; its radiance goes to the accumulator's second half (see renderer.cu)
+            int se = warp_append(out.push_env, &next[CTR_SHADOW]);
+            if (se >= 0) {
+                f.shadow.ray_ori_tmax[se] = out.env_ori_tmax;
+                f.shadow.ray_dir[se] = out.env_dir;
+                f.shadow.radiance[se] = out.env_rad;
+                f.shadow.slot[se] = idx + f.num_paths;
+            }
         }
         int ep = warp_append(out.push_ext, &next[CTR_EXT]);
         if (ep >= 0) f.q_ext[ep] = idx;
@@ -313,12 +354,50 @@ int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t
     return 1;
 }
 int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s) {
-    k_shade<MAT_PBR><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
-    k_shade<MAT_DIFFUSE><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
-    k_shade<MAT_REFLECT><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
-    k_shade<MAT_REFRACT><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    if (f.env.nee) {
+        k_shade<MAT_PBR, true><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+        k_shade<MAT_DIFFUSE, true><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    } else {
+        k_shade<MAT_PBR, false><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+        k_shade<MAT_DIFFUSE, false><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    }
+    k_shade<MAT_REFLECT, false><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
+    k_shade<MAT_REFRACT, false><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
     return 4;
 }
+// ptb_config.env_nee: the environment's shadow rays accumulate into direct[P .. 2P) so that every accumulator cell
+// still receives at most one add per bounce (a deterministic sum, bit-identical between the tile partitions); the
+// frame ends by folding that half into the direct image.
+__global__ void __launch_bounds__(256) k_fold_env(float* direct, int n3) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n3) return;
+    float e = direct[n3 + i];
+    if (e != 0.0f) {
+        direct[i] = direct[i] + e;
+        direct[n3 + i] = 0.0f;
+    }
+}
+int launch_fold_env(const FrameDev& f, cudaStream_t s) {
+    int n3 = 3 * f.num_paths;
+    k_fold_env<<<(n3 + 255) / 256, 256, 0, s>>>(f.direct, n3);
+    return 1;
+}
+
+// sampleEnvironmentMap for a batch of random pairs (ptb_sample_environment: the parity hook for the sampler)
+__global__ void __launch_bounds__(256) k_sample_environment(EnvDev env, TexturesDev tex, const float* rnd, int n, float* dir, float* pdf, int* pixel) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float p, eu, ev; int texel;
+    Vec3 d = sample_environment(env, tex, rnd[2 * i], rnd[2 * i + 1], p, texel, eu, ev);
+    dir[3 * i] = d.x; dir[3 * i + 1] = d.y; dir[3 * i + 2] = d.z;
+    pdf[i] = p;
+    pixel[i] = texel;
+}
+int launch_sample_environment(const FrameDev& f, const float* rnd, int n, float* dir, float* pdf, int* pixel, cudaStream_t s) {
+    k_sample_environment<<<(n + 255) / 256, 256, 0, s>>>(f.env, f.tex, rnd, n, dir, pdf, pixel);
+    return 1;
+}
+
 int launch_frame_end(const FrameDev& f, const LaunchCfg&, cudaStream_t s) {
     k_frame_end<<<1, 32, 0, s>>>(f);
     return 1;

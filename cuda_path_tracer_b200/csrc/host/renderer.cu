@@ -198,6 +198,7 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
         if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
     }
+    if (f.env.nee) n += launch_fold_env(f, s);
     if (r->denoiser) n += launch_svgf(f, r->svgf, r->gb, r->launch.num_sms, s);   // reads *f.iteration: before frame_end advances it
     n += launch_frame_end(f, r->launch, s);
     return n;
@@ -320,6 +321,19 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     f.tex.handles = dtex;
     f.tex.env_tex_id = scene->env.env_tex_id;
     f.tex.pdf_map_id = scene->env.pdf_map_id;
+    // the alias table the reference builds but never uploads (src/wavefront_internal.cu:206-214); see envmap.cuh
+    f.env = EnvDev{};
+    const bool have_env = scene->env.env_tex_id >= 0 && scene->env.pdf_map_id >= 0 && !scene->env.probs.empty();
+    if (have_env) {
+        float* probs; int* aliases;
+        TRY(dev_upload(r, probs, scene->env.probs.data(), scene->env.probs.size()));
+        TRY(dev_upload(r, aliases, scene->env.aliases.data(), scene->env.aliases.size()));
+        f.env.probs = probs; f.env.aliases = aliases;
+        f.env.width = scene->env.width; f.env.height = scene->env.height;
+        f.env.nee = cfg.env_nee ? 1 : 0;
+    }
+    // with env_nee a shaded path may queue two shadow rays per bounce, and the environment's land in direct[P..2P)
+    const size_t nee_factor = f.env.nee ? 2 : 1;
 
     // ---- LBVH (initBVH, src/wavefront_internal.cu:180-193 -> BuildLBVH, src/bvh.cu:456-516)
     {
@@ -371,24 +385,24 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     TRY(dev_alloc(r, f.pool.material_id, P));
     TRY(dev_alloc(r, f.pool.remaining_bounces, P));
     TRY(dev_alloc(r, f.pool.rng_state, P));
-    TRY(dev_alloc(r, f.shadow.ray_ori_tmax, P));
-    TRY(dev_alloc(r, f.shadow.ray_dir, P));
-    TRY(dev_alloc(r, f.shadow.radiance, P));
-    TRY(dev_alloc(r, f.shadow.slot, P));
+    TRY(dev_alloc(r, f.shadow.ray_ori_tmax, nee_factor * P));
+    TRY(dev_alloc(r, f.shadow.ray_dir, nee_factor * P));
+    TRY(dev_alloc(r, f.shadow.radiance, nee_factor * P));
+    TRY(dev_alloc(r, f.shadow.slot, nee_factor * P));
     TRY(dev_alloc(r, f.q_ext, P));
     for (int q = 0; q < 4; q++) TRY(dev_alloc(r, f.q_mat[q], P));
     TRY(dev_alloc(r, f.ctr, (size_t)(f.trace_depth + 1) * CTR_STRIDE));
     TRY(dev_alloc(r, f.ray_totals, 2));
     TRY(dev_alloc(r, f.iteration, 1));
     TRY(dev_alloc(r, f.error_flag, 1));
-    TRY(dev_alloc(r, f.direct, 3 * P));
+    TRY(dev_alloc(r, f.direct, nee_factor * 3 * P));
     TRY(dev_alloc(r, f.indirect, 3 * P));
     TRY(dev_alloc(r, r->cursors, kMaxTimed + 1));
     TRYCU(cudaMemsetAsync(f.ctr, 0, sizeof(int) * (f.trace_depth + 1) * CTR_STRIDE, r->stream));
     TRYCU(cudaMemsetAsync(f.ray_totals, 0, 2 * sizeof(unsigned long long), r->stream));
     TRYCU(cudaMemsetAsync(f.iteration, 0, sizeof(int), r->stream));
     TRYCU(cudaMemsetAsync(f.error_flag, 0, sizeof(int), r->stream));
-    TRYCU(cudaMemsetAsync(f.direct, 0, 3 * P * sizeof(float), r->stream));
+    TRYCU(cudaMemsetAsync(f.direct, 0, nee_factor * 3 * P * sizeof(float), r->stream));
     TRYCU(cudaMemsetAsync(f.indirect, 0, 3 * P * sizeof(float), r->stream));
     // InitPathPoolKernel (src/pathtrace_wavefront.cu:183-190): every slot starts dead
     TRYCU(cudaMemsetAsync(f.pool.remaining_bounces, 0xff, P * sizeof(int), r->stream));
@@ -599,6 +613,28 @@ int ptb_visualize_lbvh(ptb_renderer* r, void* dst, int32_t format, int32_t dst_o
     return check_device_error(r);
 }
 
+int ptb_sample_environment(ptb_renderer* r, const float* rnd, int32_t count, float* dir, float* pdf, int32_t* pixel) {
+    if (!r || !rnd || !dir || !pdf || !pixel) return fail(PTB_ERR_INVALID, "ptb_sample_environment: null argument");
+    if (count <= 0) return fail(PTB_ERR_INVALID, "ptb_sample_environment: count must be positive");
+    if (!r->frame.env.probs) return fail(PTB_ERR_STATE, "ptb_sample_environment: the scene has no environment map");
+    CU(cudaSetDevice(r->device));
+    const size_t n = (size_t)count;
+    int rc = ensure_scratch(r, n * (2 + 3 + 1 + 1) * 4);
+    if (rc) return rc;
+    float* d_rnd = (float*)r->scratch;
+    float* d_dir = d_rnd + 2 * n;
+    float* d_pdf = d_dir + 3 * n;
+    int* d_pix = (int*)(d_pdf + n);
+    CU(cudaMemcpyAsync(d_rnd, rnd, n * 8, cudaMemcpyHostToDevice, r->stream));
+    r->kernel_launches += launch_sample_environment(r->frame, d_rnd, count, d_dir, d_pdf, d_pix, r->stream);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(dir, d_dir, n * 12, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaMemcpyAsync(pdf, d_pdf, n * 4, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaMemcpyAsync(pixel, d_pix, n * 4, cudaMemcpyDeviceToHost, r->stream));
+    CU(cudaStreamSynchronize(r->stream));
+    return PTB_OK;
+}
+
 int ptb_get_tile_info(const ptb_renderer* r, ptb_tile_info* out) {
     if (!r || !out) return fail(PTB_ERR_INVALID, "ptb_get_tile_info: null argument");
     out->width = r->frame.tile.width;
@@ -778,6 +814,7 @@ int ptb_stage_run(ptb_renderer* r, int32_t stage, int32_t iteration) {
         case PTB_STAGE_TRACE:
             if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
             r->kernel_launches += launch_trace(f, r->stage_bounce, r->launch, r->stream);
+            if (f.env.nee) r->kernel_launches += launch_fold_env(f, r->stream);
             break;
         case PTB_STAGE_LOGIC:
             if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");

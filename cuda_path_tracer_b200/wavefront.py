@@ -117,13 +117,14 @@ class Scene:
 class Renderer:
     """An opaque ptb_renderer: PathtraceInit / Pathtrace / PathtraceFree on a handle."""
 
-    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False, denoiser=False):
+    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False, denoiser=False, env_nee=False):
         cfg = capi.Config()
         lib.ptb_config_default(C.byref(cfg))
         cfg.device, cfg.trace_depth, cfg.rank, cfg.world, cfg.stripe_rows = device, trace_depth, rank, world, stripe_rows
         cfg.use_graph = 1 if use_graph else 0
         cfg.gbuffer = 1 if gbuffer else 0
         cfg.denoiser = 1 if denoiser else 0
+        cfg.env_nee = 1 if env_nee else 0
         self._h = C.c_void_p()
         check(lib.ptb_init(scene._h, C.byref(cfg), C.byref(self._h)))
         t = capi.TileInfo()
@@ -134,6 +135,14 @@ class Renderer:
     # -- Pathtrace(pbo, frame, iter) --------------------------------------------------------------
     def render(self, iteration, count=1):
         check(lib.ptb_render_many(self._h, iteration, count))
+
+    def sample_environment(self, rnd):
+        """sampleEnvironmentMap for rnd[n, 2] -> (dir[n, 3], pdf[n], texel[n])."""
+        rnd = np.ascontiguousarray(rnd, dtype=np.float32).reshape(-1, 2)
+        n = rnd.shape[0]
+        d, p, t = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+        check(lib.ptb_sample_environment(self._h, ptr(rnd), n, ptr(d), ptr(p), ptr(t)))
+        return d, p, t
 
     def clear(self):
         """Zero the accumulators (what iteration 1 does implicitly); for sample-index partitions."""

@@ -154,7 +154,12 @@ typedef struct ptb_config {
     int32_t denoiser;        /* 1: SVGF (src/kernels/svgf.cu) as in the reference's DenoiserOn mode: every frame is a fresh 1-spp
                                 estimate (accumulators cleared per frame, src/pathtrace_wavefront.cu:231-236), filtered into the
                                 final image; implies gbuffer; iteration 1 restarts the history; world must be 1 */
-    int32_t reserved[6];
+    int32_t env_nee;         /* 1: next-event estimation of the HDR environment through the alias table (sampleEnvironmentMap,
+                                src/interactions.cu:447-488): the half of the environment's MIS pair the reference's Logic already
+                                assumes (src/kernels/logic.cu:88-100) but nothing in the reference runs.  CHANGES THE IMAGE: surfaces
+                                lit by the environment gain the missing energy, the indirect image and the light sampling stay bit
+                                for bit what they are with 0 (default = the reference's result).  No effect without an environment. */
+    int32_t reserved[5];
 } ptb_config;
 void ptb_config_default(ptb_config* cfg);
 
@@ -204,6 +209,11 @@ int ptb_get_gbuffer(ptb_renderer* r, int32_t which, void* dst, size_t bytes);
  * reference's blue-to-red colour (PTB_IMG_SUM_RGB32F, float3, = its d_final_image) or as the raw count
  * (PTB_IMG_STEPS_I32).  Replaces the GL "Show BVH Heatmap" view (src/preview.cpp:159). */
 int ptb_visualize_lbvh(ptb_renderer* r, void* dst, int32_t format, int32_t dst_on_device);
+
+/* sampleEnvironmentMap (src/interactions.cu:447-488) for `count` pairs of uniform numbers rnd[2*count] (host): the
+ * sampled directions dir[3*count], their solid-angle pdfs pdf[count] and the chosen texels pixel[count] (host).  What
+ * ptb_config.env_nee draws from; PTB_ERR_STATE when the scene has no environment map. */
+int ptb_sample_environment(ptb_renderer* r, const float* rnd, int32_t count, float* dir, float* pdf, int32_t* pixel);
 /* Raw accumulators (WavefrontPathTracerState::d_direct_image / d_indirect_image,
  * src/wavefront_internal.h:26-27) copied to host, 3 floats per owned pixel; either may be NULL. */
 int ptb_get_accumulators(ptb_renderer* r, float* direct, float* indirect);

@@ -71,3 +71,13 @@ def raygen_seeds(first, count, iteration):
     jx, jy = np.zeros(count, np.float32), np.zeros(count, np.float32)
     _lib.ptb_oracle_raygen_seeds(first, count, iteration, _p(rng), _p(jx), _p(jy))
     return rng, jx, jy
+
+
+def sample_environment(probs, aliases, pdf_map, width, height, rnd):
+    """sampleEnvironmentMap (src/interactions.cu:447-488) on the host-built alias table."""
+    probs = np.ascontiguousarray(probs, np.float32); aliases = np.ascontiguousarray(aliases, np.int32)
+    pdf_map = np.ascontiguousarray(pdf_map, np.float32); rnd = np.ascontiguousarray(rnd, np.float32).reshape(-1, 2)
+    n = rnd.shape[0]
+    d, p, t = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.int32)
+    _lib.ptb_oracle_sample_environment(_p(probs), _p(aliases), _p(pdf_map), int(width), int(height), _p(rnd), n, _p(d), _p(p), _p(t))
+    return d, p, t
