@@ -55,7 +55,7 @@ class SceneInfo(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("device", C.c_int32), ("trace_depth", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
-                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("denoiser", C.c_int32), ("env_nee", C.c_int32), ("reserved", C.c_int32 * 5)]
+                ("stripe_rows", C.c_int32), ("use_graph", C.c_int32), ("gbuffer", C.c_int32), ("denoiser", C.c_int32), ("env_nee", C.c_int32), ("megakernel", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class TileInfo(C.Structure):

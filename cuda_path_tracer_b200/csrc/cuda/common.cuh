@@ -210,4 +210,25 @@ struct CameraDev {               // Camera, src/scene_structs.h:16-26 (members t
     float pixel_length[2];
 };
 
+// Queue position -> path slot.  The reference fills its first queue in pixel order (queue[i] = i,
+// src/kernels/ray_gen.cu:76), so a warp of RayCast gets a 32x1 run of pixels.  Queue ORDER is unobservable
+// (every per-path result is independent of its position), so the first queue is laid out in 8x4 pixel tiles
+// instead: a warp's rays span a quarter of the width, stay on nearby surfaces for the following bounces, and
+// touch fewer distinct BVH records per load -- which is what bounds RayCast (L1 wavefronts).
+// Pixels outside the largest (8k x 4m) region keep their linear order.
+__device__ __forceinline__ int tiled_slot(int i, int width, int rows) {
+    const int w8 = width & ~7, h4 = rows & ~3;
+    const int tiled = w8 * h4;
+    if (i >= tiled) {
+        int j = i - tiled;                                   // right strip (rows < h4), then the bottom rows
+        int strip = (width - w8) * h4;
+        if (j < strip) { int sw = width - w8; return (j / sw) * width + w8 + (j % sw); }
+        return h4 * width + (j - strip);
+    }
+    int tile = i >> 5, lane = i & 31;
+    int tiles_per_row = w8 >> 3;
+    int ty = tile / tiles_per_row, tx = tile - ty * tiles_per_row;
+    return (ty * 4 + (lane >> 3)) * width + tx * 8 + (lane & 7);
+}
+
 }  // namespace ptb

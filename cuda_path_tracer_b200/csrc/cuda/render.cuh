@@ -81,6 +81,8 @@ int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t
 int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
 int launch_fold_env(const FrameDev& f, cudaStream_t s);
 int launch_sample_environment(const FrameDev& f, const float* rnd, int n, float* dir, float* pdf, int* pixel, cudaStream_t s);
+// ptb_config.megakernel (megakernel.cu): counters reset + the whole frame in one kernel
+int launch_megakernel(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);
 int launch_frame_end(const FrameDev& f, const LaunchCfg& c, cudaStream_t s);                   // ray statistics
 int launch_resolve(const FrameDev& f, void* dst, int format, int iteration, cudaStream_t s);
 // headless views (views.cu)

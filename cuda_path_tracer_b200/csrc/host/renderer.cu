@@ -172,6 +172,11 @@ static Mat4 camera_view_proj(const ptb_camera& c) {
 static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
     const FrameDev& f = r->frame;
     int n = 0;
+    if (r->cfg.megakernel) {   // pathtrace_megakernel::Pathtrace (src/pathtrace.cu:645-706): the frame is one kernel
+        n += launch_megakernel(f, r->launch, s);
+        n += launch_frame_end(f, r->launch, s);
+        return n;
+    }
     // with the denoiser every frame is a fresh 1-spp estimate (src/pathtrace_wavefront.cu:231-236)
     if (r->denoiser) n += launch_clear_accumulators(f, s);
     n += launch_raygen(f, r->launch, s);
@@ -259,6 +264,8 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     if (cfg.world < 1) cfg.world = 1;
     if (cfg.stripe_rows < 1) cfg.stripe_rows = 8;
     if (cfg.rank < 0 || cfg.rank >= cfg.world) return fail(PTB_ERR_INVALID, "ptb_init: rank outside [0, world)");
+    if (cfg.megakernel && (cfg.gbuffer || cfg.denoiser || cfg.env_nee))
+        return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the megakernel path has no G-buffer, denoiser or environment NEE (src/pathtrace.cu has none)");
     const int N = (int)scene->indices_matid.size();
     const int V = (int)scene->pos.size();
     if (N < 2) return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the LBVH needs at least 2 triangles (the reference's hierarchy is undefined below that)");
@@ -799,6 +806,7 @@ extern "C" {
 
 int ptb_stage_run(ptb_renderer* r, int32_t stage, int32_t iteration) {
     if (!r) return fail(PTB_ERR_INVALID, "ptb_stage_run: null renderer");
+    if (r->cfg.megakernel) return fail(PTB_ERR_STATE, "ptb_stage_run: the megakernel path has no stages");
     CU(cudaSetDevice(r->device));
     const FrameDev& f = r->frame;
     switch (stage) {

@@ -117,7 +117,7 @@ class Scene:
 class Renderer:
     """An opaque ptb_renderer: PathtraceInit / Pathtrace / PathtraceFree on a handle."""
 
-    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False, denoiser=False, env_nee=False):
+    def __init__(self, scene, device=0, trace_depth=0, rank=0, world=1, stripe_rows=8, use_graph=True, gbuffer=False, denoiser=False, env_nee=False, megakernel=False):
         cfg = capi.Config()
         lib.ptb_config_default(C.byref(cfg))
         cfg.device, cfg.trace_depth, cfg.rank, cfg.world, cfg.stripe_rows = device, trace_depth, rank, world, stripe_rows
@@ -125,6 +125,7 @@ class Renderer:
         cfg.gbuffer = 1 if gbuffer else 0
         cfg.denoiser = 1 if denoiser else 0
         cfg.env_nee = 1 if env_nee else 0
+        cfg.megakernel = 1 if megakernel else 0   # pathtrace_megakernel::Pathtrace (src/pathtrace.cu:645-706)
         self._h = C.c_void_p()
         check(lib.ptb_init(scene._h, C.byref(cfg), C.byref(self._h)))
         t = capi.TileInfo()

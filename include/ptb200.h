@@ -159,7 +159,15 @@ typedef struct ptb_config {
                                 assumes (src/kernels/logic.cu:88-100) but nothing in the reference runs.  CHANGES THE IMAGE: surfaces
                                 lit by the environment gain the missing energy, the indirect image and the light sampling stay bit
                                 for bit what they are with 0 (default = the reference's result).  No effect without an environment. */
-    int32_t reserved[5];
+    int32_t megakernel;      /* 1: render with the reference's OTHER path, pathtrace_megakernel::Pathtrace (src/pathtrace.cu:645-706):
+                                one kernel carries each path through all bounces.  It is a different estimator, not only a
+                                different schedule (own seeding, mirrored camera x axis, unweighted environment hits, NEE that
+                                advances the path's random stream; src/pathtrace.cu:234-452), so its image is the reference
+                                MEGAKERNEL's image, not the wavefront's.  The sample sum lands in the direct accumulator
+                                (its d_image), the indirect one stays zero; ptb_resolve divides by the iteration, which equals the
+                                reference's per-pixel sample count for iterations 1..n.  Not combinable with gbuffer, denoiser,
+                                env_nee or the staged API (PTB_ERR_UNSUPPORTED / PTB_ERR_STATE). */
+    int32_t reserved[4];
 } ptb_config;
 void ptb_config_default(ptb_config* cfg);
 

@@ -24,6 +24,10 @@ bool g_enableVisualization = false;   // extern in the reference (pathtrace_wave
 namespace pathtrace_wavefront {
     WavefrontPathTracerState* OracleState() { return pState; }
 }
+namespace pathtrace_megakernel {   // ref_mega_access.cu
+    glm::vec3* OracleImage();
+    int* OracleSampleCount();
+}
 
 static std::string g_out;
 
@@ -244,6 +248,17 @@ int main(int argc, char** argv) {
     if (mega) {
         pathtrace_megakernel::InitDataContainer(&gui);
         pathtrace_megakernel::PathtraceInit(scene);
+        if (bench_k == 0) {
+            // --mega without --bench: the float image of the reference's megakernel after `iters` samples (src/pathtrace.cu:446-451)
+            for (int i = 1; i <= iters; i++) pathtrace_megakernel::Pathtrace(NULL, 0, i);
+            cudaDeviceSynchronize();
+            dump_dev("mega_image", pathtrace_megakernel::OracleImage(), sizeof(glm::vec3) * P);
+            dump_dev("mega_samples", pathtrace_megakernel::OracleSampleCount(), sizeof(int) * P);
+            cudaError_t e = cudaGetLastError();
+            printf("REFDUMP {\"mode\": \"mega\", \"iters\": %d, \"pixels\": %d, \"mrays_per_s\": %.3f, \"cuda\": \"%s\"}\n", iters, P, gui.MraysPerSec, cudaGetErrorString(e));
+            pathtrace_megakernel::PathtraceFree();
+            return e == cudaSuccess ? 0 : 4;
+        }
         double mr = 0;
         for (int i = 1; i <= bench_w; i++) pathtrace_megakernel::Pathtrace(NULL, 0, i);
         cudaDeviceSynchronize();

@@ -18,7 +18,7 @@ def have_refdump():
     return os.path.exists(REFDUMP) and os.access(REFDUMP, os.X_OK)
 
 
-def run_refdump(scene_json, out_dir, iters=1, stages=True, selfcheck=False, timeout=900, views=False, denoise=False):
+def run_refdump(scene_json, out_dir, iters=1, stages=True, selfcheck=False, timeout=900, views=False, denoise=False, mega=False):
     os.makedirs(out_dir, exist_ok=True)
     cmd = [REFDUMP, scene_json, out_dir, "--iters", str(iters)]
     if stages:
@@ -29,6 +29,8 @@ def run_refdump(scene_json, out_dir, iters=1, stages=True, selfcheck=False, time
         cmd.append("--views")
     if denoise:
         cmd.append("--denoise")
+    if mega:   # the reference's megakernel front-end: dumps mega_image / mega_samples only
+        cmd = [REFDUMP, scene_json, out_dir, "--iters", str(iters), "--mega"]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
     if p.returncode != 0:
         raise RuntimeError(f"refdump failed ({p.returncode}):\n{p.stdout[-2000:]}\n{p.stderr[-2000:]}")
