@@ -293,6 +293,9 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
         r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);
         r->launch.overlap_shadow = knob("PTB_OVERLAP_SHADOW", 1);
+        r->launch.mega_regen = knob("PTB_MEGA_REGEN", 1);
+        r->launch.mega_refill = knob("PTB_MEGA_REFILL", 1);
+        r->launch.mega_blocks = knob("PTB_MEGA_BLOCKS", 10);
         if (r->launch.overlap_shadow) {
             TRYCU(cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking));
             TRYCU(cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming));

@@ -420,3 +420,77 @@ def test_env_nee_flag(tmp_path):
     assert mean_off < 0.9 * expect, (mean_off, expect)
     for r in (off, on, on2): r.free()
     scene.free()
+
+
+# ---- the megakernel path (ptb_config.megakernel; reference: pathtrace_megakernel::Pathtrace, src/pathtrace.cu:645-706) ----
+def _mega_ref(scene_json, d, iters):
+    par.run_refdump(scene_json, d, iters=iters, mega=True)
+    img = np.fromfile(os.path.join(d, "mega_image.bin"), dtype="<f4").reshape(-1, 3)
+    cnt = np.fromfile(os.path.join(d, "mega_samples.bin"), dtype="<i4")
+    return img, cnt
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which,iters", [("cornell", 1), ("cornell", 3), ("fire_small", 2), ("sponza_small", 2)])
+def test_megakernel_vs_reference(which, iters, fire_small, sponza_small, tmp_path):
+    """The float image of the reference's own megakernel (d_image after `iters` samples, dumped by refdump --mega) against
+    the direct accumulator of a megakernel renderer: bit for bit.  Cornell: diffuse + light; fire_small: the four material
+    models, MIS + NEE; sponza_small: MTL materials, textures, normal maps and the (unweighted) HDR environment."""
+    _need_ref()
+    scene_json = {"cornell": lambda: scenegen.cornell(str(tmp_path / "c"), res=(200, 160)), "fire_small": lambda: fire_small,
+                  "sponza_small": lambda: sponza_small}[which]()
+    ref, cnt = _mega_ref(scene_json, str(tmp_path / "ref"), iters)
+    assert (cnt == iters).all()           # the reference's per-pixel sample count is the iteration (ptb_resolve divides by it)
+    r = ptb.Renderer(ptb.Scene(scene_json), megakernel=True)
+    r.render(1, iters)
+    d, i = r.accumulators()
+    assert (i == 0).all()                 # everything lands in the direct accumulator (the reference's single d_image)
+    assert par.count_bit_mismatch(d, ref) == 0
+    mean = r.resolve(iters)
+    assert _bits(mean, d / np.float32(iters))
+    st = r.stats()
+    assert st.frames == iters and st.extension_rays >= iters * ref.shape[0] and st.kernel_launches > 0
+    r.free()
+
+
+@pytest.mark.gpu
+def test_megakernel_full_size_vs_reference(fire_full, tmp_path):
+    """BASELINE config[1] through the megakernel path: 143,173 triangles, 1920x1080, 8 bounces, 2 spp."""
+    _need_ref()
+    ref, cnt = _mega_ref(fire_full, str(tmp_path / "ref"), 2)
+    r = ptb.Renderer(ptb.Scene(fire_full), megakernel=True)
+    r.render(1, 2)
+    d, _ = r.accumulators()
+    rel = np.abs(d - ref) / np.maximum(np.abs(ref), 1e-6)
+    assert rel.max() <= 1e-4                                 # north_star tolerance
+    assert par.count_bit_mismatch(d, ref) == 0               # what is actually met
+    r.free()
+
+
+@pytest.mark.gpu
+def test_megakernel_tile_partition_and_modes(fire_small):
+    """Tiles of a megakernel frame are bit-identical to the full frame (global pixel indices seed the paths); the graph and
+    plain-launch forms agree; the options the reference's megakernel does not have are rejected."""
+    s = ptb.Scene(fire_small)
+    full = ptb.Renderer(s, megakernel=True)
+    full.render(1, 2)
+    ref, _ = full.accumulators()
+    out = np.zeros_like(ref)
+    for rank in range(3):
+        t = ptb.Renderer(s, megakernel=True, rank=rank, world=3, stripe_rows=8)
+        t.render(1, 2)
+        d, _ = t.accumulators()
+        out[t.owned_pixel_indices()] = d
+        t.free()
+    assert _bits(out, ref)
+    plain = ptb.Renderer(s, megakernel=True, use_graph=False)
+    plain.render(1, 2)
+    assert _bits(plain.accumulators()[0], ref)
+    with pytest.raises(capi.PtbError) as e:
+        plain.stage(capi.STAGE_RAYGEN, 1)
+    assert e.value.code == capi.ERR_STATE
+    for kw in ({"gbuffer": True}, {"denoiser": True}, {"env_nee": True}):
+        with pytest.raises(capi.PtbError) as e:
+            ptb.Renderer(s, megakernel=True, **kw)
+        assert e.value.code == capi.ERR_UNSUPPORTED
+    full.free(); plain.free()
