@@ -156,7 +156,12 @@ struct BvhDev {
     const float4* tri;
     float4 root_min, root_max;   // AABB of node 0 (the root test of src/kernels/ray_cast.cu:40-47)
     int num_triangles;
+    // 4-wide collapse of the same tree with 15-bit boxes (wide.cuh); wcell = (root_max - root_min) / PTB_WIDE_GRID
+    const uint4* wnode;
+    float wcell[3];
 };
+#define PTB_WIDE_GRID 32760.0f      /* quantisation steps across the scene box; +-2 steps of margin stay below 2^15 */
+#define PTB_WIDE_EMPTY 0x7fffffff   /* link of an unused child slot */
 
 struct TexturesDev {
     const cudaTextureObject_t* handles;

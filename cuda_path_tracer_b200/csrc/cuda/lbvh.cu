@@ -366,6 +366,70 @@ __global__ void __launch_bounds__(256) k_pack(LbvhBuffers b, const float4* __res
     }
 }
 
+// 4-wide traversal nodes (BvhDev::wnode, wide.cuh).  Node i is binary node i with its two children replaced, greedily
+// by surface area, by THEIR children until four are held (Wald et al.'s collapse; the tree, and therefore every leaf's
+// ancestor chain, stays the LBVH's -- only intermediate boxes are skipped).  Child boxes are stored on a 15-bit grid
+// over the scene box, rounded outwards with one extra step of margin on either side, so that the box the traversal
+// reconstructs (one fma per plane, wide.cuh) always contains the fp32 box of the reference:
+//   wnode[4*i+0] = lo.x[4] hi.x[4] (u16 each)   wnode[4*i+1] = lo.y[4] hi.y[4]   wnode[4*i+2] = lo.z[4] hi.z[4]
+//   wnode[4*i+3] = link[4]: >= 0 internal node, < 0 ~(sorted leaf position), PTB_WIDE_EMPTY unused slot (box inverted)
+__device__ __forceinline__ float box_area(float4 mn, float4 mx) {
+    float dx = mx.x - mn.x, dy = mx.y - mn.y, dz = mx.z - mn.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+__global__ void __launch_bounds__(256) k_pack_wide(LbvhBuffers b) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = b.num_triangles;
+    if (i >= n - 1) return;
+    int child[4];
+    int count = 2;
+    {
+        int2 ch = b.ref.child_nodes[i];
+        child[0] = decode_node(ch.x);
+        child[1] = decode_node(ch.y);
+    }
+    while (count < 4) {
+        int best = -1;
+        float best_area = -1.0f;
+        for (int k = 0; k < count; k++) {
+            if (child[k] >= n) continue;                      // a leaf cannot be opened
+            float a = box_area(b.ref.aabb_min[child[k]], b.ref.aabb_max[child[k]]);
+            if (a > best_area) { best_area = a; best = k; }
+        }
+        if (best < 0) break;
+        int2 ch = b.ref.child_nodes[child[best]];
+        child[best] = decode_node(ch.x);
+        child[count++] = decode_node(ch.y);
+    }
+    const float4 wmin = b.ref.aabb_min[0], wmax = b.ref.aabb_max[0];
+    const float cell[3] = {__fdiv_rn(wmax.x - wmin.x, PTB_WIDE_GRID), __fdiv_rn(wmax.y - wmin.y, PTB_WIDE_GRID), __fdiv_rn(wmax.z - wmin.z, PTB_WIDE_GRID)};
+    const float org[3] = {wmin.x, wmin.y, wmin.z};
+    unsigned int lo[3][4], hi[3][4];
+    int link[4];
+    for (int k = 0; k < 4; k++) {
+        if (k >= count) {
+            link[k] = PTB_WIDE_EMPTY;
+            for (int a = 0; a < 3; a++) { lo[a][k] = 32767u; hi[a][k] = 0u; }
+            continue;
+        }
+        const int c = child[k];
+        link[k] = c >= n ? ~(c - n) : c;
+        float4 mn = b.ref.aabb_min[c], mx = b.ref.aabb_max[c];
+        const float vmin[3] = {mn.x, mn.y, mn.z}, vmax[3] = {mx.x, mx.y, mx.z};
+        for (int a = 0; a < 3; a++) {
+            float inv_cell = cell[a] > 0.0f ? 1.0f / cell[a] : 0.0f;           // a flat scene box: every plane is step 0
+            float ql = floorf((vmin[a] - org[a]) * inv_cell) - 2.0f;
+            float qh = ceilf((vmax[a] - org[a]) * inv_cell) + 2.0f;
+            lo[a][k] = (unsigned int)fminf(fmaxf(ql, 0.0f), 32767.0f);
+            hi[a][k] = (unsigned int)fminf(fmaxf(qh, 0.0f), 32767.0f);
+        }
+    }
+    uint4* out = b.wnode + 4 * (size_t)i;
+    for (int a = 0; a < 3; a++)
+        out[a] = make_uint4(lo[a][0] | (lo[a][1] << 16), lo[a][2] | (lo[a][3] << 16), hi[a][0] | (hi[a][1] << 16), hi[a][2] | (hi[a][3] << 16));
+    out[3] = make_uint4((unsigned)link[0], (unsigned)link[1], (unsigned)link[2], (unsigned)link[3]);
+}
+
 // ---- host side -------------------------------------------------------------------------------
 template <typename T>
 static cudaError_t dalloc(T*& p, size_t count, size_t& total) {
@@ -393,6 +457,7 @@ int lbvh_alloc(LbvhBuffers& b, int n) {
     A(dalloc(b.ref.world_aabb, 2, t));
     A(dalloc(b.node, 4 * (size_t)n, t));
     A(dalloc(b.tri, PTB_TRI_STRIDE * (size_t)n, t));
+    A(dalloc(b.wnode, 4 * (size_t)n, t));
     A(dalloc(b.key_a, (size_t)n, t));
     A(dalloc(b.key_b, (size_t)n, t));
     A(dalloc(b.val_b, (size_t)n, t));
@@ -408,7 +473,7 @@ int lbvh_alloc(LbvhBuffers& b, int n) {
 
 void lbvh_free(LbvhBuffers& b) {
     void* ptrs[] = {b.ref.aabb_min, b.ref.aabb_max, b.ref.centroid, b.ref.primitive_indices, b.ref.morton_codes,
-                    b.ref.child_nodes, b.ref.parent, b.ref.escape_indices, b.ref.world_aabb, b.node, b.tri,
+                    b.ref.child_nodes, b.ref.parent, b.ref.escape_indices, b.ref.world_aabb, b.node, b.tri, b.wnode,
                     b.key_a, b.key_b, b.val_b, b.counts, b.totals, b.flags, b.world_enc, b.max_depth};
     for (void* p : ptrs) if (p) cudaFree(p);
     b = LbvhBuffers{};
@@ -439,6 +504,7 @@ int lbvh_build(LbvhBuffers& b, const float4* pos, const int4* indices_matid, cud
     k_refit<<<nb, bs, 0, s>>>(b); count++;
     k_escape_depth<<<nb, bs, 0, s>>>(b); count++;
     k_pack<<<nb, bs, 0, s>>>(b, pos, indices_matid); count++;
+    k_pack_wide<<<nb, bs, 0, s>>>(b); count++;
     if (launches) *launches += count;
     return (int)cudaGetLastError();
 }

@@ -11,6 +11,7 @@ struct LbvhBuffers {
     // traversal layout (see BvhDev in common.cuh)
     float4* node = nullptr;      // 4 * (N-1)
     float4* tri = nullptr;       // PTB_TRI_STRIDE * N
+    uint4* wnode = nullptr;      // 4 * (N-1): 4-wide quantised nodes (BvhDev::wnode), indexed by the binary node they collapse
     // scratch kept for rebuilds
     unsigned int* key_a = nullptr;   // 30-bit Morton codes, ping
     unsigned int* key_b = nullptr;   // pong

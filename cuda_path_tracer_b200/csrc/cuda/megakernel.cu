@@ -23,6 +23,7 @@
 #include "bsdf.cuh"
 #include "logic.cuh"
 #include "raycast.cuh"
+#include "wide.cuh"
 #include "render.cuh"
 
 namespace ptb {
@@ -116,7 +117,7 @@ __device__ __forceinline__ void mega_start(const FrameDev& f, int iter, int rows
 
 // One iteration of the reference's depth loop (:283-440) for the path on this lane.  Returns false when the path ended
 // (miss, emitter, dead sample, or the bounce budget).
-template <int STACK>
+template <int STACK, bool WIDE>
 __device__ __forceinline__ bool mega_bounce(const FrameDev& f, MegaPath& p, int* my_stack, int& n_ext, int& n_shadow) {
     n_ext++;
     Hit hit = mega_closest<STACK>(f.bvh, p.ray_ori, p.ray_dir, my_stack, PTB_MEGA_THREADS);
@@ -198,7 +199,8 @@ __device__ __forceinline__ bool mega_bounce(const FrameDev& f, MegaPath& p, int*
                     float t_max = dist_L - 2.0f * PTB_EPSILON;
                     n_shadow++;
                     // IsOccluded, :122-169: a leaf occludes iff eps < t < t_max - eps, boxes pass iff t_max > t_box
-                    int occ = trace_any<STACK>(f.bvh, shadow_ori, wi_L, t_max, my_stack, PTB_MEGA_THREADS);
+                    int occ = WIDE ? trace_any_exact<STACK>(f.bvh, shadow_ori, wi_L, t_max, my_stack, PTB_MEGA_THREADS)
+                                   : trace_any<STACK>(f.bvh, shadow_ori, wi_L, t_max, my_stack, PTB_MEGA_THREADS);
                     if (occ < 0) atomicExch(f.error_flag, 1);
                     if (occ == 0) p.accumulated = p.accumulated + L_potential;
                 }
@@ -239,7 +241,7 @@ __device__ __forceinline__ void mega_finish(const FrameDev& f, const MegaPath& p
 // whose path ended wait for the longest one, as in the reference).  REGEN = true: a lane whose path ended takes the
 // next pixel of the frame at once (path regeneration), so a warp stays full until the frame runs out; which lane
 // renders a pixel does not enter its arithmetic, so both give the same image.
-template <int STACK, bool REGEN>
+template <int STACK, bool REGEN, bool WIDE>
 __global__ void __launch_bounds__(PTB_MEGA_THREADS, PTB_MEGA_MINBLOCKS) k_megakernel(const __grid_constant__ FrameDev f, int refill_min) {
     __shared__ int stack[STACK * PTB_MEGA_THREADS];
     int* my_stack = stack + threadIdx.x;
@@ -259,7 +261,7 @@ __global__ void __launch_bounds__(PTB_MEGA_THREADS, PTB_MEGA_MINBLOCKS) k_megake
             const int qpos = base + lane;
             if (qpos < f.num_paths) {
                 mega_start(f, iter, rows, qpos, p);
-                while (mega_bounce<STACK>(f, p, my_stack, n_ext, n_shadow)) {}
+                while (mega_bounce<STACK, WIDE>(f, p, my_stack, n_ext, n_shadow)) {}
                 mega_finish(f, p);
             }
         }
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(PTB_MEGA_THREADS, PTB_MEGA_MINBLOCKS) k_megake
             }
             if (idle == FULL) break;
             if (active) {
-                if (!mega_bounce<STACK>(f, p, my_stack, n_ext, n_shadow)) {
+                if (!mega_bounce<STACK, WIDE>(f, p, my_stack, n_ext, n_shadow)) {
                     mega_finish(f, p);
                     active = false;
                 }
@@ -304,13 +306,17 @@ int launch_megakernel(const FrameDev& f, const LaunchCfg& c, cudaStream_t s) {
     k_mega_begin<<<1, 128, 0, s>>>(f);
     const int grid = c.num_sms * (c.mega_blocks > 0 ? c.mega_blocks : PTB_MEGA_MINBLOCKS);
     const bool deep = c.shadow_deep != 0;
+    const int refill = c.mega_regen ? c.mega_refill : 0;
+    const bool wide = (c.wide & 4) != 0;
+#define PTB_MEGA_LAUNCH(S, R, W) k_megakernel<S, R, W><<<grid, PTB_MEGA_THREADS, 0, s>>>(f, refill)
     if (c.mega_regen) {
-        if (!deep) k_megakernel<32, true><<<grid, PTB_MEGA_THREADS, 0, s>>>(f, c.mega_refill);
-        else k_megakernel<64, true><<<grid, PTB_MEGA_THREADS, 0, s>>>(f, c.mega_refill);
+        if (!deep) { if (wide) PTB_MEGA_LAUNCH(32, true, true); else PTB_MEGA_LAUNCH(32, true, false); }
+        else { if (wide) PTB_MEGA_LAUNCH(64, true, true); else PTB_MEGA_LAUNCH(64, true, false); }
     } else {
-        if (!deep) k_megakernel<32, false><<<grid, PTB_MEGA_THREADS, 0, s>>>(f, 0);
-        else k_megakernel<64, false><<<grid, PTB_MEGA_THREADS, 0, s>>>(f, 0);
+        if (!deep) { if (wide) PTB_MEGA_LAUNCH(32, false, true); else PTB_MEGA_LAUNCH(32, false, false); }
+        else { if (wide) PTB_MEGA_LAUNCH(64, false, true); else PTB_MEGA_LAUNCH(64, false, false); }
     }
+#undef PTB_MEGA_LAUNCH
     return 2;
 }
 

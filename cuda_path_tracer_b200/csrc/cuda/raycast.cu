@@ -3,6 +3,7 @@
 // warps pull 32-ray batches from the queue through a device-side cursor, and the queue length is
 // read on the device (no host round trip per bounce).
 #include "raycast.cuh"
+#include "wide.cuh"
 #include "logic.cuh"
 #include "render.cuh"
 
@@ -23,7 +24,8 @@ __device__ __forceinline__ int warp_fetch(int* cursor) {
 // FUSE_LOGIC: run the Logic stage (logic.cuh) on each path the moment its extension ray is done, while the hit
 // record is in registers -- the frame graph's form.  Without it this is the reference's TraceExtensionRay alone
 // (staged API, ptb_time_raycast).
-template <bool FUSE_LOGIC>
+// WIDE: the 4-wide quantised walk (wide.cuh) instead of trace_closest(); both give the same bits.
+template <bool FUSE_LOGIC, bool WIDE>
 __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_extension(FrameDev f, int bounce, int* cursor) {
     __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
     int* ctr = f.ctr + bounce * CTR_STRIDE;
@@ -36,7 +38,8 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_exte
             path = __ldg(&f.q_ext[i]);
             float4 o4 = f.pool.ray_ori[path];
             float4 d4 = f.pool.ray_dir_dist[path];
-            Hit h = trace_closest(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS);
+            Hit h = WIDE ? trace_closest_exact(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS)
+                         : trace_closest(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS);
             // write-back, src/kernels/ray_cast.cu:111-121
             if (h.prim == -1) {
                 f.pool.ray_dir_dist[path].w = -1.0f;
@@ -188,7 +191,7 @@ __global__ void __launch_bounds__(PTB_RC_THREADS) k_batch_closest_pl(BvhDev bvh,
     closest_persistent<false>(bvh, rays, n, work, stack + threadIdx.x, refill_min);
 }
 
-template <int STACK, bool SHARED>
+template <int STACK, bool SHARED, bool WIDE>
 __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_SH_MINBLOCKS : 1) k_trace_shadow(FrameDev f, int bounce) {
     __shared__ int sstack[SHARED ? STACK * PTB_RC_THREADS : 1];
     int lstack[SHARED ? 1 : STACK];
@@ -201,7 +204,8 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_
         if (i >= count) continue;
         float4 o4 = __ldg(&f.shadow.ray_ori_tmax[i]);
         float4 d4 = __ldg(&f.shadow.ray_dir[i]);
-        int r = trace_any<STACK>(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), o4.w, my_stack, stride);
+        int r = WIDE ? trace_any_exact<STACK>(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), o4.w, my_stack, stride)
+                     : trace_any<STACK>(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), o4.w, my_stack, stride);
         if (r == 0) {   // visible: AtomicAddVec3(&d_direct_image[pixel], radiance), :193-199
             int slot = __ldg(&f.shadow.slot[i]);
             float4 rad = __ldg(&f.shadow.radiance[i]);
@@ -218,8 +222,11 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_
 static inline int rc_grid(const LaunchCfg& c) { return c.num_sms * (c.rc_blocks > 0 ? c.rc_blocks : 8); }
 
 static void run_extension(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s, bool fuse_logic = false) {
-    if (fuse_logic) k_trace_extension<true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
-    else if (c.rc_variant == 0) k_trace_extension<false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
+    const bool wide = (c.wide & 2) != 0;
+    if (fuse_logic && wide) k_trace_extension<true, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
+    else if (fuse_logic) k_trace_extension<true, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
+    else if (wide) k_trace_extension<false, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
+    else if (c.rc_variant == 0) k_trace_extension<false, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
     else if (c.rc_variant == 1) k_trace_extension_pl<false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, c.rc_refill);
     else k_trace_extension_pl<true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, c.rc_refill);
 }
@@ -238,10 +245,14 @@ int launch_trace_shadow(const FrameDev& f, int bounce, const LaunchCfg& c, cudaS
     if (bounce == 0) return 0;   // no shadow rays exist before the first Shade (counter zeroed by RayGen, src/kernels/ray_gen.cu:121-124)
     // the DFS stack never holds more than one entry per tree level: size it from the measured LBVH depth
     const int g = rc_grid(c);
-    if (c.shadow_deep == 3) k_trace_shadow<256, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
-    else if (c.shadow_deep == 0) k_trace_shadow<32, true><<<c.num_sms * PTB_SH_MINBLOCKS, PTB_RC_THREADS, 0, s>>>(f, bounce);
-    else if (c.shadow_deep == 1) k_trace_shadow<48, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
-    else k_trace_shadow<64, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    const bool wide = (c.wide & 1) != 0;
+    if (c.shadow_deep == 3) k_trace_shadow<256, false, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (c.shadow_deep == 0 && wide) k_trace_shadow<32, true, true><<<c.num_sms * (c.sh_blocks > 0 ? c.sh_blocks : PTB_SH_MINBLOCKS), PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (c.shadow_deep == 0) k_trace_shadow<32, true, false><<<c.num_sms * PTB_SH_MINBLOCKS, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (c.shadow_deep == 1 && wide) k_trace_shadow<48, true, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (c.shadow_deep == 1) k_trace_shadow<48, true, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else if (wide) k_trace_shadow<64, true, true><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
+    else k_trace_shadow<64, true, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
     return 1;
 }
 
@@ -301,3 +312,7 @@ int launch_trace_batch_occluded(const BvhDev& bvh, const float4* ori_tmax, const
 }
 
 }  // namespace ptb
+
+#ifdef PTB_WIDE_DEBUG   // development counters of the wide walk (not part of the ABI): rays, bad reciprocal, re-traced, stack overflow
+extern "C" int ptb_debug_wide(unsigned long long* out) { return (int)cudaMemcpyFromSymbol(out, ptb::g_wide_dbg, sizeof(unsigned long long) * 8); }
+#endif

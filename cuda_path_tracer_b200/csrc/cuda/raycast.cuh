@@ -13,6 +13,13 @@
 
 namespace ptb {
 
+#ifdef PTB_WIDE_DEBUG
+static __device__ unsigned long long g_wide_dbg[8];
+#define PTB_WDBG(i) atomicAdd(&g_wide_dbg[i], 1ull)
+#else
+#define PTB_WDBG(i)
+#endif
+
 #define PTB_NODE_NONE 0x7fffffff
 #define PTB_EXT_STACK 32          /* src/kernels/ray_cast.cu:35,106 */
 #define PTB_SHADOW_STACK 64

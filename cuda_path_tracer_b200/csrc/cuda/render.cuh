@@ -65,6 +65,8 @@ struct LaunchCfg {
     int rc_blocks;            // resident blocks per SM the persistent grids are sized for
     int fuse_logic;           // frame graph: Logic runs in the tail of the extension RayCast kernel
     int overlap_shadow;       // frame graph: TraceShadow(b) runs beside TraceExtension(b) on a forked branch
+    int wide;                 // 4-wide quantised traversal (wide.cuh): bit 0 shadow rays, bit 1 extension rays, bit 2 megakernel
+    int sh_blocks;            // resident blocks per SM of the wide shadow kernel
     int mega_regen;           // megakernel: a lane whose path ended takes the next pixel at once (path regeneration)
     int mega_refill;          // megakernel: regenerate once this many lanes of a warp are idle
     int mega_blocks;          // megakernel: resident blocks per SM the persistent grid is sized for

@@ -1,0 +1,226 @@
+// wide.cuh -- traversal of the 4-wide, 15-bit-quantised collapse of the LBVH (BvhDev::wnode, built by k_pack_wide).
+//
+// Why: RayCast on B200 is bound by the L1 data pipe and the issue slots, not by HBM: every node
+// visit of the binary walk pulls a 64-byte record through L1 to test two boxes.  Here a 64-byte record holds FOUR
+// child boxes, so a ray makes about half the dependent round trips and pulls half the bytes per box tested.
+//
+// Why the results are still the reference's.  The reference tests a triangle iff every box on the leaf's ancestor chain
+// passes BoudingboxIntersetionTest (src/intersections.cu:34-61).  That test is monotone under box inclusion in fp32 (each
+// (p - o) * inv is monotone in p, min / max are monotone), so the chain passes iff the LEAF's own box passes -- and the
+// leaf's box is the min / max of the triangle's vertices (ComputeAABB, src/bvh.cu:13-35), which the leaf record holds.
+// So: inner boxes here only have to be conservative (they are: rounded outwards plus a margin larger than the
+// reconstruction error), and a triangle hit is accepted only if the reference's own test on the leaf's fp32 box passes
+// with the reference's cull (`t_box < t_best`, resp. `tmax > t_box`).  What remains order-dependent in the reference's
+// walk is which of two hits within a few ulps of each other wins (exact ties; a leaf whose fp32 box distance rounds
+// above its own hit distance can be culled by a hit that is farther by less than that).  trace_closest_wide() keeps
+// every candidate within PTB_WIDE_SLACK of the best alive, notices when two accepted hits are that close, and then
+// reports `ambiguous`; the caller re-traces such a ray (about one in 10^5) with the reference-order binary walk.
+// Rays with a zero direction component (inv = inf; the fma form would produce NaN where the reference's form does
+// not) and stack overflows take the same exit.
+#pragma once
+#include "raycast.cuh"
+
+namespace ptb {
+
+#define PTB_WIDE_SLACK 1.00001f
+#define PTB_WIDE_STACK 32
+
+struct WideRay {
+    Vec3 o, d, inv;          // inv = 1 / d (IEEE), as the reference computes it
+    float iqx, iqy, iqz;     // inv * cell: t per quantisation step
+    float bx, by, bz;        // t(q) = fma(32768 + q, iq, b)
+    unsigned sel_near_x, sel_near_y, sel_near_z;   // 0: the near plane of an axis is `lo` (inv >= 0), 1: it is `hi`
+    bool ok;                 // false: direction has a zero / non-finite reciprocal -> use the binary walk
+};
+
+__device__ __forceinline__ WideRay wide_setup(const BvhDev& bvh, Vec3 o, Vec3 d) {
+    WideRay r;
+    r.o = o; r.d = d;
+    r.inv = Vec3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+    r.iqx = r.inv.x * bvh.wcell[0]; r.iqy = r.inv.y * bvh.wcell[1]; r.iqz = r.inv.z * bvh.wcell[2];
+    r.bx = (bvh.root_min.x - o.x) * r.inv.x - 32768.0f * r.iqx;
+    r.by = (bvh.root_min.y - o.y) * r.inv.y - 32768.0f * r.iqy;
+    r.bz = (bvh.root_min.z - o.z) * r.inv.z - 32768.0f * r.iqz;
+    r.sel_near_x = r.inv.x < 0.0f; r.sel_near_y = r.inv.y < 0.0f; r.sel_near_z = r.inv.z < 0.0f;
+    const float big = 3.0e38f;
+    r.ok = fabsf(r.inv.x) < big && fabsf(r.inv.y) < big && fabsf(r.inv.z) < big &&
+           fabsf(r.bx) < big && fabsf(r.by) < big && fabsf(r.bz) < big;     // also false for NaN
+    return r;
+}
+
+// 15-bit step `k` of a packed pair -> the float 32768 + q, in one PRMT: bytes (0, q.lo, q.hi, 0x47).
+__device__ __forceinline__ float wide_plane(unsigned packed, int half) {
+    return __uint_as_float(__byte_perm(packed, 0x47000000u, half ? 0x7324 : 0x7104));
+}
+
+struct WideHits { float t[4]; };
+
+// Entry distances of the four children (max(0, t_near)), or -1 where the ray misses the box or enters beyond t_limit.
+__device__ __forceinline__ void wide_test(const WideRay& r, const uint4& qx, const uint4& qy, const uint4& qz, float t_limit, float t[4]) {
+    // near / far plane words per axis: .x/.y = lo[0..3], .z/.w = hi[0..3]
+    const unsigned nx0 = r.sel_near_x ? qx.z : qx.x, nx1 = r.sel_near_x ? qx.w : qx.y, fx0 = r.sel_near_x ? qx.x : qx.z, fx1 = r.sel_near_x ? qx.y : qx.w;
+    const unsigned ny0 = r.sel_near_y ? qy.z : qy.x, ny1 = r.sel_near_y ? qy.w : qy.y, fy0 = r.sel_near_y ? qy.x : qy.z, fy1 = r.sel_near_y ? qy.y : qy.w;
+    const unsigned nz0 = r.sel_near_z ? qz.z : qz.x, nz1 = r.sel_near_z ? qz.w : qz.y, fz0 = r.sel_near_z ? qz.x : qz.z, fz1 = r.sel_near_z ? qz.y : qz.w;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int half = k & 1;
+        const unsigned nx = (k < 2) ? nx0 : nx1, fx = (k < 2) ? fx0 : fx1;
+        const unsigned ny = (k < 2) ? ny0 : ny1, fy = (k < 2) ? fy0 : fy1;
+        const unsigned nz = (k < 2) ? nz0 : nz1, fz = (k < 2) ? fz0 : fz1;
+        float tn = fmaxf(fmaxf(fmaf(wide_plane(nx, half), r.iqx, r.bx), fmaf(wide_plane(ny, half), r.iqy, r.by)),
+                         fmaxf(fmaf(wide_plane(nz, half), r.iqz, r.bz), 0.0f));
+        float tf = fminf(fminf(fmaf(wide_plane(fx, half), r.iqx, r.bx), fmaf(wide_plane(fy, half), r.iqy, r.by)),
+                         fminf(fmaf(wide_plane(fz, half), r.iqz, r.bz), t_limit));
+        t[k] = (tn <= tf) ? tn : -1.0f;
+    }
+}
+
+// The reference's own test on the leaf's fp32 box (= min / max of the vertices, src/bvh.cu:24-25).
+__device__ __forceinline__ float leaf_box_test(float4 a, float4 b, float4 c, Vec3 o, Vec3 inv) {
+    float4 mn = make_float4(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z), 0.0f);
+    float4 mx = make_float4(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z), 0.0f);
+    return slab_test(mn, mx, o, inv);
+}
+
+#define PTB_WIDE_CSWAP(i, j)                                         \
+    {                                                                \
+        bool sw_ = key[j] < key[i];                                  \
+        float tk_ = sw_ ? key[j] : key[i];                           \
+        int tl_ = sw_ ? lnk[j] : lnk[i];                             \
+        key[j] = sw_ ? key[i] : key[j];                              \
+        lnk[j] = sw_ ? lnk[i] : lnk[j];                              \
+        key[i] = tk_;                                                \
+        lnk[i] = tl_;                                                \
+    }
+
+// Any hit.  Returns 1 occluded, 0 visible, -1: not decidable here (stack overflow), take the binary walk.
+template <int STACK>
+__device__ __forceinline__ int trace_any_wide(const BvhDev& bvh, const WideRay& r, float tmax, int* stack, int stride) {
+    const float t_limit = __fsub_rn(tmax, PTB_EPSILON);
+    int sp = 0;
+    int node = 0;
+    int result = 0;
+    // one loop, one exit: the walk ends by emptying (node, sp), so the lanes of a warp reconverge at the loop head
+    while (node != PTB_NODE_NONE || sp > 0) {
+        if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
+        if (node >= 0) {
+            const uint4* np = bvh.wnode + 4 * (size_t)node;
+            F8 a = ldg256(reinterpret_cast<const float4*>(np)), b = ldg256(reinterpret_cast<const float4*>(np + 2));
+            const uint4 qx = make_uint4(__float_as_uint(a.a.x), __float_as_uint(a.a.y), __float_as_uint(a.a.z), __float_as_uint(a.a.w));
+            const uint4 qy = make_uint4(__float_as_uint(a.b.x), __float_as_uint(a.b.y), __float_as_uint(a.b.z), __float_as_uint(a.b.w));
+            const uint4 qz = make_uint4(__float_as_uint(b.a.x), __float_as_uint(b.a.y), __float_as_uint(b.a.z), __float_as_uint(b.a.w));
+            const int lnk[4] = {__float_as_int(b.b.x), __float_as_int(b.b.y), __float_as_int(b.b.z), __float_as_int(b.b.w)};
+            float t[4];
+            wide_test(r, qx, qy, qz, tmax, t);
+            node = PTB_NODE_NONE;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (t[k] >= 0.0f) {
+                    if (node == PTB_NODE_NONE) node = lnk[k];
+                    else if (sp < STACK) stack[(sp++) * stride] = lnk[k];
+                    else result = -1;
+                }
+            }
+        } else {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
+            float u, v;
+            float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), r.o, r.d, u, v);
+            node = PTB_NODE_NONE;
+            if (t > PTB_EPSILON && t < t_limit) {
+                float tb = leaf_box_test(a, b, c, r.o, r.inv);          // the reference reaches this leaf iff its own box passes
+                if (tb != -1.0f && tmax > tb) result = 1;
+            }
+        }
+        if (result != 0) { node = PTB_NODE_NONE; sp = 0; }
+    }
+    return result;
+}
+
+// Closest hit, nearest child first.  `ambiguous` is set when the answer could depend on the reference's visiting order
+// (two accepted hits within PTB_WIDE_SLACK of each other) or the stack overflowed: the caller re-traces with trace_closest().
+template <int STACK>
+__device__ __forceinline__ Hit trace_closest_wide(const BvhDev& bvh, const WideRay& r, int* stack, int stride, bool& ambiguous) {
+    Hit h;
+    h.prim = -1; h.mat = -1; h.t = FLT_MAX; h.u = 0.0f; h.v = 0.0f;
+    float limit = FLT_MAX;          // h.t * slack
+    float second = FLT_MAX;         // nearest accepted candidate other than h
+    ambiguous = false;
+    int sp = 0;
+    int node = 0;
+    bool overflow = false;
+    while (node != PTB_NODE_NONE || sp > 0) {
+        if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
+        if (node >= 0) {
+            const uint4* np = bvh.wnode + 4 * (size_t)node;
+            F8 a = ldg256(reinterpret_cast<const float4*>(np)), b = ldg256(reinterpret_cast<const float4*>(np + 2));
+            const uint4 qx = make_uint4(__float_as_uint(a.a.x), __float_as_uint(a.a.y), __float_as_uint(a.a.z), __float_as_uint(a.a.w));
+            const uint4 qy = make_uint4(__float_as_uint(a.b.x), __float_as_uint(a.b.y), __float_as_uint(a.b.z), __float_as_uint(a.b.w));
+            const uint4 qz = make_uint4(__float_as_uint(b.a.x), __float_as_uint(b.a.y), __float_as_uint(b.a.z), __float_as_uint(b.a.w));
+            int lnk[4] = {__float_as_int(b.b.x), __float_as_int(b.b.y), __float_as_int(b.b.z), __float_as_int(b.b.w)};
+            float key[4];
+            PTB_WDBG(4);
+            wide_test(r, qx, qy, qz, limit, key);
+#pragma unroll
+            for (int k = 0; k < 4; k++) if (key[k] < 0.0f) key[k] = FLT_MAX;     // misses sort last
+            PTB_WIDE_CSWAP(0, 1) PTB_WIDE_CSWAP(2, 3) PTB_WIDE_CSWAP(0, 2) PTB_WIDE_CSWAP(1, 3) PTB_WIDE_CSWAP(1, 2)
+            // push the farther hits, farthest first
+#pragma unroll
+            for (int k = 3; k >= 1; k--) {
+                if (key[k] != FLT_MAX) {
+                    if (sp < STACK) stack[(sp++) * stride] = lnk[k];
+                    else overflow = true;
+                }
+            }
+            node = (key[0] != FLT_MAX) ? lnk[0] : PTB_NODE_NONE;
+        } else {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
+            float u, v;
+            float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), r.o, r.d, u, v);
+            PTB_WDBG(5);
+            if (t > PTB_EPSILON && t < limit) {
+                float tb = leaf_box_test(a, b, c, r.o, r.inv);
+                if (tb != -1.0f && tb < limit) {
+                    if (t < h.t && tb < h.t) {                       // the reference's acceptance, src/kernels/ray_cast.cu:68,93-94
+                        second = fminf(second, h.t);
+                        h.t = t; h.u = u; h.v = v;
+                        h.prim = __float_as_int(a.w);
+                        h.mat = __float_as_int(b.w);
+                        limit = h.t * PTB_WIDE_SLACK;
+                    } else {
+                        second = fminf(second, t);
+                    }
+                }
+            }
+            node = PTB_NODE_NONE;
+        }
+        if (overflow) { node = PTB_NODE_NONE; sp = 0; }
+    }
+    ambiguous = overflow || ((h.prim != -1) && (second <= limit));
+    return h;
+}
+
+// The two walks behind one call: wide first, the reference-order binary walk where the wide one cannot vouch for the result.
+__device__ __forceinline__ Hit trace_closest_exact(const BvhDev& bvh, Vec3 o, Vec3 d, int* stack, int stride) {
+    WideRay r = wide_setup(bvh, o, d);
+    bool ambiguous = true;
+    Hit h;
+    PTB_WDBG(0);
+    if (!r.ok) PTB_WDBG(1);
+    if (r.ok) h = trace_closest_wide<PTB_WIDE_STACK>(bvh, r, stack, stride, ambiguous);
+    if (ambiguous) { PTB_WDBG(2); h = trace_closest(bvh, o, d, stack, stride); }
+    return h;
+}
+template <int STACK>
+__device__ __forceinline__ int trace_any_exact(const BvhDev& bvh, Vec3 o, Vec3 d, float tmax, int* stack, int stride) {
+    WideRay r = wide_setup(bvh, o, d);
+    int res = -1;
+    if (r.ok) res = trace_any_wide<STACK>(bvh, r, tmax, stack, stride);
+    if (res < 0) res = trace_any<STACK>(bvh, o, d, tmax, stack, stride);
+    return res;
+}
+
+}  // namespace ptb

@@ -293,6 +293,8 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
         r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);
         r->launch.overlap_shadow = knob("PTB_OVERLAP_SHADOW", 1);
+        r->launch.wide = knob("PTB_WIDE", 1);
+        r->launch.sh_blocks = knob("PTB_SH_BLOCKS", 12);
         r->launch.mega_regen = knob("PTB_MEGA_REGEN", 1);
         r->launch.mega_refill = knob("PTB_MEGA_REFILL", 1);
         r->launch.mega_blocks = knob("PTB_MEGA_BLOCKS", 10);
@@ -369,6 +371,11 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         TRYCU(cudaMemcpy(&root[1], r->lbvh.ref.aabb_max, sizeof(float4), cudaMemcpyDeviceToHost));
         f.bvh.node = r->lbvh.node;
         f.bvh.tri = r->lbvh.tri;
+        f.bvh.wnode = r->lbvh.wnode;
+        // the quantisation step k_pack_wide used: (root_max - root_min) / PTB_WIDE_GRID, IEEE division on both sides
+        f.bvh.wcell[0] = (root[1].x - root[0].x) / PTB_WIDE_GRID;
+        f.bvh.wcell[1] = (root[1].y - root[0].y) / PTB_WIDE_GRID;
+        f.bvh.wcell[2] = (root[1].z - root[0].z) / PTB_WIDE_GRID;
         f.bvh.root_min = root[0];
         f.bvh.root_max = root[1];
         f.bvh.num_triangles = N;
