@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(256) k_pack(LbvhBuffers b, const float4* __res
 // ancestor chain, stays the LBVH's -- only intermediate boxes are skipped).  Child boxes are stored on a 15-bit grid
 // over the scene box, rounded outwards with one extra step of margin on either side, so that the box the traversal
 // reconstructs (one fma per plane, wide.cuh) always contains the fp32 box of the reference:
-//   wnode[4*i+0] = lo.x[4] hi.x[4] (u16 each)   wnode[4*i+1] = lo.y[4] hi.y[4]   wnode[4*i+2] = lo.z[4] hi.z[4]
+//   wnode[4*i+a] (a = x, y, z) = four words, one per child: lo_a | hi_a << 16 (15-bit steps)
 //   wnode[4*i+3] = link[4]: >= 0 internal node, < 0 ~(sorted leaf position), PTB_WIDE_EMPTY unused slot (box inverted)
 __device__ __forceinline__ float box_area(float4 mn, float4 mx) {
     float dx = mx.x - mn.x, dy = mx.y - mn.y, dz = mx.z - mn.z;
@@ -426,7 +426,7 @@ __global__ void __launch_bounds__(256) k_pack_wide(LbvhBuffers b) {
     }
     uint4* out = b.wnode + 4 * (size_t)i;
     for (int a = 0; a < 3; a++)
-        out[a] = make_uint4(lo[a][0] | (lo[a][1] << 16), lo[a][2] | (lo[a][3] << 16), hi[a][0] | (hi[a][1] << 16), hi[a][2] | (hi[a][3] << 16));
+        out[a] = make_uint4(lo[a][0] | (hi[a][0] << 16), lo[a][1] | (hi[a][1] << 16), lo[a][2] | (hi[a][2] << 16), lo[a][3] | (hi[a][3] << 16));
     out[3] = make_uint4((unsigned)link[0], (unsigned)link[1], (unsigned)link[2], (unsigned)link[3]);
 }
 

@@ -24,12 +24,14 @@ namespace ptb {
 
 #define PTB_WIDE_SLACK 1.00001f
 #define PTB_WIDE_STACK 32
+#define PTB_WIDE_SEL_LO 0x7104u   /* PRMT selectors, see wide_plane() */
+#define PTB_WIDE_SEL_HI 0x7324u
 
 struct WideRay {
     Vec3 o, d, inv;          // inv = 1 / d (IEEE), as the reference computes it
     float iqx, iqy, iqz;     // inv * cell: t per quantisation step
     float bx, by, bz;        // t(q) = fma(32768 + q, iq, b)
-    unsigned sel_near_x, sel_near_y, sel_near_z;   // 0: the near plane of an axis is `lo` (inv >= 0), 1: it is `hi`
+    unsigned near_x, near_y, near_z;   // PRMT selector of an axis' near plane: the `lo` half of a child's word if inv >= 0, else `hi`
     bool ok;                 // false: direction has a zero / non-finite reciprocal -> use the binary walk
 };
 
@@ -41,36 +43,33 @@ __device__ __forceinline__ WideRay wide_setup(const BvhDev& bvh, Vec3 o, Vec3 d)
     r.bx = (bvh.root_min.x - o.x) * r.inv.x - 32768.0f * r.iqx;
     r.by = (bvh.root_min.y - o.y) * r.inv.y - 32768.0f * r.iqy;
     r.bz = (bvh.root_min.z - o.z) * r.inv.z - 32768.0f * r.iqz;
-    r.sel_near_x = r.inv.x < 0.0f; r.sel_near_y = r.inv.y < 0.0f; r.sel_near_z = r.inv.z < 0.0f;
+    r.near_x = r.inv.x < 0.0f ? PTB_WIDE_SEL_HI : PTB_WIDE_SEL_LO;
+    r.near_y = r.inv.y < 0.0f ? PTB_WIDE_SEL_HI : PTB_WIDE_SEL_LO;
+    r.near_z = r.inv.z < 0.0f ? PTB_WIDE_SEL_HI : PTB_WIDE_SEL_LO;
     const float big = 3.0e38f;
     r.ok = fabsf(r.inv.x) < big && fabsf(r.inv.y) < big && fabsf(r.inv.z) < big &&
            fabsf(r.bx) < big && fabsf(r.by) < big && fabsf(r.bz) < big;     // also false for NaN
     return r;
 }
 
-// 15-bit step `k` of a packed pair -> the float 32768 + q, in one PRMT: bytes (0, q.lo, q.hi, 0x47).
-__device__ __forceinline__ float wide_plane(unsigned packed, int half) {
-    return __uint_as_float(__byte_perm(packed, 0x47000000u, half ? 0x7324 : 0x7104));
+// A child's word holds lo | hi << 16 (15-bit steps).  One PRMT turns either half into the float 32768 + q:
+// bytes (0, q.lo, q.hi, 0x47); the selector picks the half, so the ray's octant costs no extra instruction.
+__device__ __forceinline__ float wide_plane(unsigned word, unsigned sel) {
+    return __uint_as_float(__byte_perm(word, 0x47000000u, sel));
 }
-
-struct WideHits { float t[4]; };
 
 // Entry distances of the four children (max(0, t_near)), or -1 where the ray misses the box or enters beyond t_limit.
 __device__ __forceinline__ void wide_test(const WideRay& r, const uint4& qx, const uint4& qy, const uint4& qz, float t_limit, float t[4]) {
-    // near / far plane words per axis: .x/.y = lo[0..3], .z/.w = hi[0..3]
-    const unsigned nx0 = r.sel_near_x ? qx.z : qx.x, nx1 = r.sel_near_x ? qx.w : qx.y, fx0 = r.sel_near_x ? qx.x : qx.z, fx1 = r.sel_near_x ? qx.y : qx.w;
-    const unsigned ny0 = r.sel_near_y ? qy.z : qy.x, ny1 = r.sel_near_y ? qy.w : qy.y, fy0 = r.sel_near_y ? qy.x : qy.z, fy1 = r.sel_near_y ? qy.y : qy.w;
-    const unsigned nz0 = r.sel_near_z ? qz.z : qz.x, nz1 = r.sel_near_z ? qz.w : qz.y, fz0 = r.sel_near_z ? qz.x : qz.z, fz1 = r.sel_near_z ? qz.y : qz.w;
+    const unsigned far_x = r.near_x ^ 0x0220u, far_y = r.near_y ^ 0x0220u, far_z = r.near_z ^ 0x0220u;
+    const unsigned wx[4] = {qx.x, qx.y, qx.z, qx.w}, wy[4] = {qy.x, qy.y, qy.z, qy.w}, wz[4] = {qz.x, qz.y, qz.z, qz.w};
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        const int half = k & 1;
-        const unsigned nx = (k < 2) ? nx0 : nx1, fx = (k < 2) ? fx0 : fx1;
-        const unsigned ny = (k < 2) ? ny0 : ny1, fy = (k < 2) ? fy0 : fy1;
-        const unsigned nz = (k < 2) ? nz0 : nz1, fz = (k < 2) ? fz0 : fz1;
-        float tn = fmaxf(fmaxf(fmaf(wide_plane(nx, half), r.iqx, r.bx), fmaf(wide_plane(ny, half), r.iqy, r.by)),
-                         fmaxf(fmaf(wide_plane(nz, half), r.iqz, r.bz), 0.0f));
-        float tf = fminf(fminf(fmaf(wide_plane(fx, half), r.iqx, r.bx), fmaf(wide_plane(fy, half), r.iqy, r.by)),
-                         fminf(fmaf(wide_plane(fz, half), r.iqz, r.bz), t_limit));
+        float tn = fmaxf(fmaxf(fmaf(wide_plane(wx[k], r.near_x), r.iqx, r.bx), fmaf(wide_plane(wy[k], r.near_y), r.iqy, r.by)),
+                         fmaf(wide_plane(wz[k], r.near_z), r.iqz, r.bz));
+        float tf = fminf(fminf(fmaf(wide_plane(wx[k], far_x), r.iqx, r.bx), fmaf(wide_plane(wy[k], far_y), r.iqy, r.by)),
+                         fmaf(wide_plane(wz[k], far_z), r.iqz, r.bz));
+        tn = fmaxf(tn, 0.0f);
+        tf = fminf(tf, t_limit);
         t[k] = (tn <= tf) ? tn : -1.0f;
     }
 }
