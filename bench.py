@@ -82,10 +82,16 @@ def reference_arm(args, rank):
         return
     rb = json.loads(line[0][len("REFBENCH "):])
     v = rb["mpaths_per_s"]
+    # the reference's other front-end on the same files (secondary figure; the headline metric is the wavefront path)
+    pm = subprocess.run([REFDUMP, scene, "/tmp/ptb_bench_ref", "--no-dump", "--bench", str(args.steps), str(args.warmup), "--mega"],
+                        capture_output=True, text=True, timeout=3000)
+    lm = [l for l in pm.stdout.splitlines() if l.startswith("REFBENCH")]
+    mega = json.loads(lm[0][len("REFBENCH "):]) if lm else None
     print(json.dumps({"impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
                       "ms_per_step": rb["ms_per_frame"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                       "config": {"workload": WORKLOAD, "reference": "s64zxu/CUDA-Path-Tracer wavefront build recompiled -arch=sm_100 (oracle/Makefile), Pathtrace(NULL,0,iter) loop, wall clock around the loop",
-                                 "mrays_per_s": rb["mrays_per_s"]},
+                                 "mrays_per_s": rb["mrays_per_s"],
+                                 "megakernel_path": None if mega is None else {"ms_per_frame": mega["ms_per_frame"], "mpaths_per_s": mega["mpaths_per_s"], "mrays_per_s": mega["mrays_per_s"]}},
                       "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": 0, "kind": "reference",
                                        "sample": "the reference has no CPU implementation of this path (SURVEY.md fact 2): this arm is its own CUDA build on one B200; the CPU port is timed in the main arm"},
                       "e2e": {"value": v, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -271,9 +277,25 @@ def main():
                 torch.cuda.synchronize()
         barrier()
         e2e_s = allmax(time.perf_counter() - t0)
-        roof = cpu = None
+        roof = cpu = mega_info = None
         if not args.no_extras:
             roof, cpu = roofline_and_cpu(r, scene, world, rank, rays / (args.steps * P * world))
+            if world == 1:
+                # secondary figure: the same frame through the OTHER render path (ptb_config.megakernel; the reference's
+                # pathtrace_megakernel::Pathtrace, src/pathtrace.cu:645-706), timed the same way
+                rm = ptb.Renderer(scene, device=local_rank, megakernel=True)
+                rm.set_stream(stream.cuda_stream)
+
+                def mega_step(k):
+                    rm.render(k + 1)
+                    rm.resolve_device(tile.data_ptr(), k + 1)
+                    return tile
+                mms = timed(mega_step, 0) / args.steps
+                sm = rm.stats()
+                mega_info = {"what": "ptb_config.megakernel = 1: one persistent kernel per frame with the reference megakernel's estimator (bit-exact vs its d_image, tests/test_gpu_parity.py)",
+                             "ms_per_frame": round(mms, 4), "mpaths_per_s": round(P / mms / 1e3, 3),
+                             "rays_per_path": round((sm.extension_rays + sm.shadow_rays) / (sm.frames * P), 3)}
+                rm.free()
     paths_per_step = P * world
     if rank == 0:
         ms = total_ms / args.steps
@@ -293,6 +315,8 @@ def main():
             out["cpu_baseline"] = cpu
         if tile_info is not None:
             out["config"]["tile_partition"] = tile_info
+        if mega_info is not None:
+            out["config"]["megakernel_path"] = mega_info
         print(json.dumps(out))
     r.free()
     if world > 1:
