@@ -33,6 +33,14 @@ def test_struct_layouts():
     assert C.sizeof(capi.Material) == 48          # reference Material, src/scene_structs.h:52-65
     assert C.sizeof(capi.Camera) == 4 * (2 + 3 * 5 + 2 + 2)
     assert C.sizeof(capi.Config) == 4 * 14
+    # field order of ptb_config (include/ptb200.h) and the defaults: wavefront path, full frame, graph on, every option off
+    assert [f[0] for f in capi.Config._fields_] == ["device", "trace_depth", "rank", "world", "stripe_rows", "use_graph", "gbuffer", "denoiser",
+                                                    "env_nee", "megakernel", "reserved"]
+    cfg = capi.Config()
+    C.memset(C.byref(cfg), 0xff, C.sizeof(cfg))
+    capi.lib.ptb_config_default(C.byref(cfg))
+    assert (cfg.device, cfg.trace_depth, cfg.rank, cfg.world, cfg.stripe_rows, cfg.use_graph) == (0, 0, 0, 1, 8, 1)
+    assert (cfg.gbuffer, cfg.denoiser, cfg.env_nee, cfg.megakernel, list(cfg.reserved)) == (0, 0, 0, 0, [0, 0, 0, 0])
 
 
 @pytest.mark.parametrize("case,gen", [("cornell64", lambda d: scenegen.cornell(d, res=(64, 64))),
