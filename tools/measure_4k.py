@@ -14,12 +14,18 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import cuda_path_tracer_b200 as ptb
 from cuda_path_tracer_b200 import multigpu, scenegen
 
-SPP, RES, STRIPE = int(os.environ.get("SPP", "64")), (3840, 2160), 8
+# SCENE=stress: BASELINE config 4 instead (10,000,000-triangle height field from arrays, 1920x1080, 4 spp)
+STRESS = os.environ.get("SCENE", "sponza") == "stress"
+SPP, RES, STRIPE = int(os.environ.get("SPP", "4" if STRESS else "64")), ((1920, 1080) if STRESS else (3840, 2160)), 8
 rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
 if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-scene = ptb.Scene(scenegen.sponza(f"/tmp/m4k_{rank}", res=RES)[0])
+if STRESS:
+    pos, nor, idx, mat = scenegen.heightfield_arrays(10_000_000)
+    scene = ptb.Scene.from_arrays(pos, nor, idx, mat, scenegen.stress_materials(), scenegen.stress_camera(RES))
+else:
+    scene = ptb.Scene(scenegen.sponza(f"/tmp/m4k_{rank}", res=RES)[0])
 W, H = RES
 stream = torch.cuda.Stream()
 with torch.cuda.stream(stream):
@@ -52,7 +58,7 @@ with torch.cuda.stream(stream):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     if rank == 0:
-        out = {"config": "5: 3840x2160, %d spp, 262,279-triangle textured scene" % SPP, "n_gpus": world, "ms": round(float(ms[0]), 2),
+        out = {"config": ("4: 1920x1080, %d spp, 10,000,000-triangle stress scene" if STRESS else "5: 3840x2160, %d spp, 262,279-triangle textured scene") % SPP, "n_gpus": world, "ms": round(float(ms[0]), 2),
                "mpaths_per_s": round(W * H * SPP / float(ms[0]) / 1e3, 1), "partition": f"interleaved {STRIPE}-row stripes, one gather"}
         if world > 1:
             one = ptb.Renderer(scene, device=local)
