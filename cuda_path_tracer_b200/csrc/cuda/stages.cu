@@ -221,8 +221,11 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
 
 // One kernel per material queue: a queue's launch carries only its own model's registers and local frame (the
 // four models in one kernel cost 95 registers and an 864-byte frame per thread, most of it dead for any given warp).
+// 8 resident blocks per SM (64 registers, 24 bytes of spills) instead of the 4 that the natural 121 registers allow: the
+// kernel waits on scattered path-state and mesh loads (ncu: issue slots 21 % busy at 25 % occupancy), more warps hide
+// more of it: 143k scene 12.53 -> 12.40 ms, textured scene 7.98 -> 7.56 ms per frame, same bits (6: 12.80, 10: 12.59).
 #ifndef PTB_SHADE_MINBLOCKS
-#define PTB_SHADE_MINBLOCKS 1
+#define PTB_SHADE_MINBLOCKS 8
 #endif
 template <int TYPE, bool ENV>
 __global__ void __launch_bounds__(kThreads, PTB_SHADE_MINBLOCKS) k_shade(const __grid_constant__ FrameDev f, int bounce) {
