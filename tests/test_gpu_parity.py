@@ -494,3 +494,42 @@ def test_megakernel_tile_partition_and_modes(fire_small):
             ptb.Renderer(s, megakernel=True, **kw)
         assert e.value.code == capi.ERR_UNSUPPORTED
     full.free(); plain.free()
+
+
+# ---- the 4-wide quantised tree (wide.cuh) against the binary walk ------------------------------------------------------
+def _render_with(env, make, iters=2):
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)          # the traversal knobs are read once, in ptb_init
+    try:
+        r = make()
+        r.render(1, iters)
+        d, i = r.accumulators()
+        r.free()
+        return d, i
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["fire_small", "sponza_small", "heightfield_2m"])
+def test_wide_tree_matches_binary_walk(which, fire_small, sponza_small):
+    """Shadow rays (the default), extension rays and the megakernel's visibility rays on the 4-wide 15-bit-quantised collapse of
+    the LBVH give the accumulators of the binary walk bit for bit: inner boxes are only conservative, a hit is accepted through
+    the reference's test on the leaf's fp32 box, near-ties are re-traced in reference order.  The
+    height field is the hard case for the quantisation: 2 M triangles, a triangle is 23 grid steps wide, +-2 steps of margin."""
+    if which == "heightfield_2m":
+        pos, nor, idx, mat = scenegen.heightfield_arrays(2_000_000)
+        scene = ptb.Scene.from_arrays(pos, nor, idx, mat, scenegen.stress_materials(), scenegen.stress_camera((640, 360)))
+    else:
+        scene = ptb.Scene({"fire_small": fire_small, "sponza_small": sponza_small}[which])
+    ref = _render_with({"PTB_WIDE": "0"}, lambda: ptb.Renderer(scene))
+    for bits in ("1", "2", "3"):
+        got = _render_with({"PTB_WIDE": bits}, lambda: ptb.Renderer(scene))
+        assert _bits(got[0], ref[0]) and _bits(got[1], ref[1]), f"PTB_WIDE={bits}"
+    mref = _render_with({"PTB_WIDE": "0"}, lambda: ptb.Renderer(scene, megakernel=True))
+    mgot = _render_with({"PTB_WIDE": "4"}, lambda: ptb.Renderer(scene, megakernel=True))
+    assert _bits(mgot[0], mref[0])
