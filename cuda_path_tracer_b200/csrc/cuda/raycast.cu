@@ -56,140 +56,8 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_exte
     }
 }
 
-// ---- persistent lanes: while-while traversal with refill ------------------------------------------------------------
-// Every ray still walks the tree in its own reference order (near child first, leaf tested the moment it is reached),
-// so results are bit-identical to trace_closest(); what changes is how rays are scheduled onto lanes:
-//   * a warp owns a CHUNK of the queue (one atomicAdd per chunk) and hands rays to lanes with ballot/popc,
-//   * one node per lane per iteration (leaf or internal), exactly like trace_closest(),
-//   * lanes whose ray ended write the hit record at once and are refilled once `refill_min` lanes are idle,
-//     so a warp never idles 31 lanes waiting for its longest ray.
-// (A while-while split -- all lanes descend to a leaf, then test together -- was measured 1.4-2.4x SLOWER here:
-// without speculative descent the lanes wait on the longest chain, and the if/else form lets the two sides of a
-// diverged warp overlap each other's load latency.)
-#define PTB_RC_CHUNK 128
-
-struct ExtRays {                 // extension queue of one bounce -> path pool (src/kernels/ray_cast.cu:17-24,111-121)
-    FrameDev f;
-    __device__ __forceinline__ int load(int i, Vec3& o, Vec3& d) const {
-        int path = __ldg(&f.q_ext[i]);
-        float4 o4 = f.pool.ray_ori[path], d4 = f.pool.ray_dir_dist[path];
-        o = Vec3(o4.x, o4.y, o4.z); d = Vec3(d4.x, d4.y, d4.z);
-        return path;
-    }
-    __device__ __forceinline__ void store(int path, const Hit& h) const {
-        if (h.prim == -1) {
-            f.pool.ray_dir_dist[path].w = -1.0f;
-            f.pool.hit_geom_id[path] = -1;
-        } else {
-            f.pool.ray_dir_dist[path].w = h.t;
-            f.pool.material_id[path] = h.mat;
-            f.pool.hit_geom_id[path] = h.prim;
-            f.pool.hit_uv[path] = make_float4(h.u, h.v, 0.0f, 0.0f);
-        }
-    }
-};
-
-struct BatchRays {               // caller arrays (ptb_trace_closest)
-    const float4 *ori, *dir;
-    int* hit; float *t, *u, *v;
-    __device__ __forceinline__ int load(int i, Vec3& o, Vec3& d) const {
-        float4 o4 = __ldg(&ori[i]), d4 = __ldg(&dir[i]);
-        o = Vec3(o4.x, o4.y, o4.z); d = Vec3(d4.x, d4.y, d4.z);
-        return i;
-    }
-    __device__ __forceinline__ void store(int i, const Hit& h) const {
-        hit[i] = h.prim; t[i] = h.prim == -1 ? -1.0f : h.t; u[i] = h.u; v[i] = h.v;
-    }
-};
-
-template <bool PREFETCH, class Rays>
-__device__ __forceinline__ void closest_persistent(const BvhDev& bvh, const Rays& rays, int count, int* cursor, int* my_stack, int refill_min) {
-    const unsigned FULL = 0xffffffffu;
-    const unsigned lt_mask = (1u << (threadIdx.x & 31)) - 1u;
-    const int stride = PTB_RC_THREADS;
-    int chunk_next = 0, chunk_end = 0;
-    bool exhausted = false, active = false;
-    Vec3 o, d, inv;
-    Hit h;
-    int node = PTB_NODE_NONE, sp = 0, token = 0;
-    h.prim = -1; h.mat = -1; h.t = FLT_MAX; h.u = 0.0f; h.v = 0.0f;
-    for (;;) {
-        unsigned idle = __ballot_sync(FULL, !active);
-        if (idle == FULL || (!exhausted && __popc(idle) >= refill_min)) {
-            if (chunk_next >= chunk_end && !exhausted) {
-                int base = 0;
-                if ((threadIdx.x & 31) == 0) base = atomicAdd(cursor, PTB_RC_CHUNK);
-                base = __shfl_sync(FULL, base, 0);
-                if (base >= count) exhausted = true;
-                else { chunk_next = base; chunk_end = min(base + PTB_RC_CHUNK, count); }
-            }
-            int avail = chunk_end - chunk_next;
-            if (avail > 0) {
-                int r = __popc(idle & lt_mask);
-                if (!active && r < avail) {
-                    token = rays.load(chunk_next + r, o, d);
-                    inv = Vec3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
-                    h.prim = -1; h.mat = -1; h.t = FLT_MAX; h.u = 0.0f; h.v = 0.0f;
-                    sp = 0;
-                    node = (slab_test(bvh.root_min, bvh.root_max, o, inv) == -1.0f) ? PTB_NODE_NONE : 0;
-                    active = true;
-                }
-                chunk_next += min(__popc(idle), avail);
-            } else if (idle == FULL) {
-                break;                                  // queue drained and no lane has a ray
-            }
-        }
-        if (active) {
-            if (node == PTB_NODE_NONE) node = my_stack[(--sp) * stride];     // active => node valid or sp > 0
-            if (node < 0) {
-                const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
-                F8 ab = ldg256(tp);
-                float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
-                float u, v;
-                float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, u, v);
-                if (t > PTB_EPSILON && t < h.t) {
-                    h.t = t; h.u = u; h.v = v;
-                    h.prim = __float_as_int(a.w);
-                    h.mat = __float_as_int(b.w);
-                }
-                node = PTB_NODE_NONE;
-            } else {
-                const float4* np = bvh.node + 4 * (size_t)node;
-                F8 nl = ldg256(np), nr = ldg256(np + 2);
-                float4 n0 = nl.a, n1 = nl.b, n2 = nr.a, n3 = nr.b;
-                int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
-                float t_l = slab_test(n0, n1, o, inv);
-                float t_r = slab_test(n2, n3, o, inv);
-                bool hit_l = (t_l != -1.0f && t_l < h.t);
-                bool hit_r = (t_r != -1.0f && t_r < h.t);
-                if (hit_l && hit_r) {
-                    bool left_first = t_l < t_r;
-                    my_stack[(sp++) * stride] = left_first ? right : left;
-                    node = left_first ? left : right;
-                    if (sp >= PTB_EXT_STACK) { node = PTB_NODE_NONE; sp = 0; }   // :106 -- the reference gives up here
-                } else if (hit_l) node = left;
-                else if (hit_r) node = right;
-                else node = PTB_NODE_NONE;
-            }
-            if (node == PTB_NODE_NONE && sp == 0) {     // the ray has ended
-                rays.store(token, h);
-                active = false;
-            }
-        }
-    }
-}
-
-template <bool PREFETCH>
-__global__ void __launch_bounds__(PTB_RC_THREADS) k_trace_extension_pl(FrameDev f, int bounce, int* cursor, int refill_min) {
-    __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
-    ExtRays rays{f};
-    closest_persistent<PREFETCH>(f.bvh, rays, f.ctr[bounce * CTR_STRIDE + CTR_EXT], cursor, stack + threadIdx.x, refill_min);
-}
-
-__global__ void __launch_bounds__(PTB_RC_THREADS) k_batch_closest_pl(BvhDev bvh, BatchRays rays, int n, int* work, int refill_min) {
-    __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
-    closest_persistent<false>(bvh, rays, n, work, stack + threadIdx.x, refill_min);
-}
+// (A persistent-lane scheduler -- a warp owns a chunk of the queue and refills lanes whose ray ended -- was measured
+// 1.3-1.4x slower than one 32-ray batch per warp fetch and is no longer part of the build)
 
 template <int STACK, bool SHARED, bool WIDE>
 __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_SH_MINBLOCKS : 1) k_trace_shadow(FrameDev f, int bounce) {
@@ -226,9 +94,7 @@ static void run_extension(const FrameDev& f, int bounce, int* cursor, const Laun
     if (fuse_logic && wide) k_trace_extension<true, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
     else if (fuse_logic) k_trace_extension<true, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
     else if (wide) k_trace_extension<false, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
-    else if (c.rc_variant == 0) k_trace_extension<false, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
-    else if (c.rc_variant == 1) k_trace_extension_pl<false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, c.rc_refill);
-    else k_trace_extension_pl<true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, c.rc_refill);
+    else k_trace_extension<false, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
 }
 
 int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s) {
@@ -298,8 +164,7 @@ __global__ void __launch_bounds__(PTB_RC_THREADS) k_batch_occluded(BvhDev bvh, c
 int launch_trace_batch_closest(const BvhDev& bvh, const float4* ori, const float4* dir, int n, int* hit, float* t, float* u,
                                float* v, int* work, const LaunchCfg& c, cudaStream_t s) {
     cudaMemsetAsync(work, 0, sizeof(int), s);
-    if (c.rc_variant == 0) k_batch_closest<<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(bvh, ori, dir, n, hit, t, u, v, work);
-    else k_batch_closest_pl<<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(bvh, BatchRays{ori, dir, hit, t, u, v}, n, work, c.rc_refill);
+    k_batch_closest<<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(bvh, ori, dir, n, hit, t, u, v, work);
     return 1;
 }
 

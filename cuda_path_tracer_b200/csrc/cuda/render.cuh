@@ -60,8 +60,6 @@ struct FrameDev {
 struct LaunchCfg {
     int num_sms;
     int shadow_deep;          // shadow-stack class from the LBVH depth: 0: <= 32, 1: <= 48, 2: <= 64 (shared memory), 3: <= 256 (local)
-    int rc_variant;           // RayCast scheduling: 0 = one 32-ray batch per warp fetch, 1 = persistent lanes with refill
-    int rc_refill;            // variant 1: refill once this many lanes of a warp are idle
     int rc_blocks;            // resident blocks per SM the persistent grids are sized for
     int fuse_logic;           // frame graph: Logic runs in the tail of the extension RayCast kernel
     int overlap_shadow;       // frame graph: TraceShadow(b) runs beside TraceExtension(b) on a forked branch

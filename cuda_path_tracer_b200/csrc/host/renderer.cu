@@ -288,8 +288,6 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     r->launch.num_sms = prop.multiProcessorCount;
     {   // tuning knobs of the RayCast scheduler (defaults are the measured best; env overrides are for A/B runs only)
         auto knob = [](const char* name, int def) { const char* e = std::getenv(name); return e ? std::atoi(e) : def; };
-        r->launch.rc_variant = knob("PTB_RC_VARIANT", 0);
-        r->launch.rc_refill = knob("PTB_RC_REFILL", 8);
         r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
         r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);
         r->launch.overlap_shadow = knob("PTB_OVERLAP_SHADOW", 1);

@@ -1,5 +1,7 @@
-"""A/B of the RayCast scheduler knobs on the bench scene (GPU box): per-bounce k_trace_extension time, frame time,
-and bit-equality of the path state after every TRACE stage against variant 0."""
+"""A/B of the RayCast knobs on the bench scene (GPU box): per-bounce k_trace_extension time, frame time, and bit-equality
+of the path state after every TRACE stage against the first configuration.  Knobs are the PTB_* environment overrides
+ptb_init reads (PTB_RC_BLOCKS, PTB_WIDE, PTB_FUSE_LOGIC, PTB_OVERLAP_SHADOW, PTB_SH_BLOCKS); pass them as
+`PTB_WIDE=3,PTB_RC_BLOCKS=8` arguments.  (The persistent-lane scheduler this tool was first written for has been removed.)"""
 import os
 import sys
 import time
@@ -10,15 +12,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import cuda_path_tracer_b200 as ptb
 from cuda_path_tracer_b200 import capi, scenegen
 
-configs = [dict(PTB_RC_VARIANT=0)] + [dict(PTB_RC_VARIANT=1, PTB_RC_REFILL=r, PTB_RC_BLOCKS=b) for r, b in
-                                        [(1, 8), (4, 8), (8, 8), (16, 8), (24, 8), (32, 8), (8, 10), (16, 10)]]
+configs = [dict(PTB_WIDE=1), dict(PTB_WIDE=0), dict(PTB_WIDE=3), dict(PTB_WIDE=1, PTB_RC_BLOCKS=8)]
 if len(sys.argv) > 1:
     configs = [dict(kv.split("=") for kv in a.split(",") if kv) for a in sys.argv[1:]]
 scene = ptb.Scene(scenegen.fireplace("/tmp/rc_ab_fire", res=(1920, 1080))[0])
 base = None
 for cfg in configs:
     for k in list(os.environ):
-        if k.startswith("PTB_RC_") or k.startswith("PTB_SH_"):
+        if k.startswith("PTB_"):
             del os.environ[k]
     os.environ.update({k: str(v) for k, v in cfg.items()})
     r = ptb.Renderer(scene)
