@@ -88,6 +88,9 @@ __device__ __forceinline__ Hit trace_closest(const BvhDev& bvh, Vec3 o, Vec3 d, 
     int node = (slab_test(bvh.root_min, bvh.root_max, o, inv) == -1.0f) ? PTB_NODE_NONE : 0;
     while (node != PTB_NODE_NONE || sp > 0) {
         if (node == PTB_NODE_NONE) node = stack[(--sp) * stride];
+#ifdef PTB_WIDE_DEBUG   // live lanes of this warp-iteration, in bins of 4 (tools/lane_hist.py)
+        { unsigned m_ = __activemask(); if ((threadIdx.x & 31) == __ffs(m_) - 1) atomicAdd(&g_wide_dbg[(__popc(m_) - 1) >> 2], 1ull); }
+#endif
         if (node < 0) {
             const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
             F8 ab = ldg256(tp);
