@@ -533,3 +533,27 @@ def test_wide_tree_matches_binary_walk(which, fire_small, sponza_small):
     mref = _render_with({"PTB_WIDE": "0"}, lambda: ptb.Renderer(scene, megakernel=True))
     mgot = _render_with({"PTB_WIDE": "4"}, lambda: ptb.Renderer(scene, megakernel=True))
     assert _bits(mgot[0], mref[0])
+
+
+# ---- ragged sizes: resolutions that are not multiples of the 8x4 queue tile, short and long bounce budgets -------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("res,depth", [((201, 163), 3), ((67, 5), 1), ((8, 4), 8), ((333, 2), 12)])
+def test_ragged_resolution_and_depth_vs_reference(res, depth, tmp_path):
+    """The first queue is laid out in 8x4 pixel tiles with a right strip and bottom rows in linear order (tiled_slot); the frame
+    graph has 4 * depth - 2 kernel nodes.  Both render paths against the reference's own builds on resolutions that exercise every
+    branch of that layout and on trace depths 1, 3, 8 and 12: bit for bit."""
+    _need_ref()
+    scene_json = scenegen.cornell(str(tmp_path / "c"), res=res, depth=depth)
+    d = str(tmp_path / "ref")
+    par.run_refdump(scene_json, d, iters=2, stages=False)
+    ref = par.RefDump(d)
+    r = ptb.Renderer(ptb.Scene(scene_json))
+    r.render(1, 2)
+    dn, inn = r.accumulators()
+    assert par.count_bit_mismatch(dn, ref.load("direct", "<f4", 3)) == 0 and par.count_bit_mismatch(inn, ref.load("indirect", "<f4", 3)) == 0
+    r.free()
+    mref, cnt = _mega_ref(scene_json, str(tmp_path / "mref"), 2)
+    m = ptb.Renderer(ptb.Scene(scene_json), megakernel=True)
+    m.render(1, 2)
+    assert par.count_bit_mismatch(m.accumulators()[0], mref) == 0
+    m.free()
