@@ -299,6 +299,8 @@ __global__ void __launch_bounds__(256) k_refit(LbvhBuffers b) {
     int n = b.num_triangles;
     if (tid >= n) return;
     int cur = tid + n;
+    // the climbing thread keeps the box of the node it came from in registers and reads only the sibling's
+    float4 cmin = b.ref.aabb_min[cur], cmax = b.ref.aabb_max[cur];
     while (true) {
         int parent = b.ref.parent[cur];
         if (parent == -1) break;
@@ -306,10 +308,12 @@ __global__ void __launch_bounds__(256) k_refit(LbvhBuffers b) {
         if (atomicAdd(&b.flags[parent], 1) == 0) return;
         int2 ch = b.ref.child_nodes[parent];
         int lc = decode_node(ch.x), rc = decode_node(ch.y);
-        float4 lmin = __ldcg(&b.ref.aabb_min[lc]), lmax = __ldcg(&b.ref.aabb_max[lc]);
-        float4 rmin = __ldcg(&b.ref.aabb_min[rc]), rmax = __ldcg(&b.ref.aabb_max[rc]);
-        b.ref.aabb_min[parent] = make_float4(fminf(lmin.x, rmin.x), fminf(lmin.y, rmin.y), fminf(lmin.z, rmin.z), fminf(lmin.w, rmin.w));
-        b.ref.aabb_max[parent] = make_float4(fmaxf(lmax.x, rmax.x), fmaxf(lmax.y, rmax.y), fmaxf(lmax.z, rmax.z), fmaxf(lmax.w, rmax.w));
+        int sib = (lc == cur) ? rc : lc;
+        float4 smin = __ldcg(&b.ref.aabb_min[sib]), smax = __ldcg(&b.ref.aabb_max[sib]);
+        cmin = make_float4(fminf(cmin.x, smin.x), fminf(cmin.y, smin.y), fminf(cmin.z, smin.z), fminf(cmin.w, smin.w));
+        cmax = make_float4(fmaxf(cmax.x, smax.x), fmaxf(cmax.y, smax.y), fmaxf(cmax.z, smax.z), fmaxf(cmax.w, smax.w));
+        b.ref.aabb_min[parent] = cmin;
+        b.ref.aabb_max[parent] = cmax;
         cur = parent;
     }
 }
