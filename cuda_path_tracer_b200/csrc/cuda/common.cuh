@@ -172,15 +172,33 @@ struct TexturesDev {
 // PathState (src/scene_structs.h:97-117).  Slot == index into this renderer's owned pixels; the
 // GLOBAL pixel index (what seeds the RNG and what the reference calls pixel_idx) is derived from
 // the slot by TileMap, so it is not stored.
+// Storage is three interleaved records per slot, so that the fields a stage reads together share 32-byte sectors (a
+// scattered 16-byte or 4-byte read costs a whole sector of DRAM / L2 traffic either way):
+//   ray [2*slot + 0] = ray_ori        ray [2*slot + 1] = ray_dir_dist      (RayCast reads both, Shade rewrites both)
+//   surf[2*slot + 0] = hit_uv         surf[2*slot + 1] = throughput_pdf    (Logic / Shade read both)
+//   meta[slot] = (hit_geom_id, material_id, remaining_bounces, rng_state)
+// The members below are thin views with operator[], so kernels keep the reference's field names.
+struct PoolF4 {                  // every second float4 of an interleaved array
+    float4* base;
+    __device__ __forceinline__ float4& operator[](int i) const { return base[2 * (size_t)i]; }
+};
+template <typename T>
+struct PoolI {                   // one 32-bit component of the int4 `meta` records
+    T* base;
+    __device__ __forceinline__ T& operator[](int i) const { return base[4 * (size_t)i]; }
+};
 struct PathPool {
-    float4* ray_ori;
-    float4* ray_dir_dist;
-    float4* hit_uv;              // the reference's `hit_normal`: (u, v, 0, 0) (src/kernels/ray_cast.cu:120)
-    float4* throughput_pdf;
-    int* hit_geom_id;
-    int* material_id;
-    int* remaining_bounces;
-    uint32_t* rng_state;
+    PoolF4 ray_ori;
+    PoolF4 ray_dir_dist;
+    PoolF4 hit_uv;               // the reference's `hit_normal`: (u, v, 0, 0) (src/kernels/ray_cast.cu:120)
+    PoolF4 throughput_pdf;
+    PoolI<int> hit_geom_id;
+    PoolI<int> material_id;
+    PoolI<int> remaining_bounces;
+    PoolI<uint32_t> rng_state;
+    float4* ray;                 // [2 * P]
+    float4* surf;                // [2 * P]
+    int4* meta;                  // [P]
 };
 
 struct ShadowQueueDev {          // ShadowQueue, src/scene_structs.h:121-131

@@ -392,14 +392,17 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     f.num_paths = (int)P;
     f.trace_depth = cfg.trace_depth > 0 ? cfg.trace_depth : scene->trace_depth;
     if (f.trace_depth < 1) f.trace_depth = 1;
-    TRY(dev_alloc(r, f.pool.ray_ori, P));
-    TRY(dev_alloc(r, f.pool.ray_dir_dist, P));
-    TRY(dev_alloc(r, f.pool.hit_uv, P));
-    TRY(dev_alloc(r, f.pool.throughput_pdf, P));
-    TRY(dev_alloc(r, f.pool.hit_geom_id, P));
-    TRY(dev_alloc(r, f.pool.material_id, P));
-    TRY(dev_alloc(r, f.pool.remaining_bounces, P));
-    TRY(dev_alloc(r, f.pool.rng_state, P));
+    TRY(dev_alloc(r, f.pool.ray, 2 * P));
+    TRY(dev_alloc(r, f.pool.surf, 2 * P));
+    TRY(dev_alloc(r, f.pool.meta, P));
+    f.pool.ray_ori.base = f.pool.ray;
+    f.pool.ray_dir_dist.base = f.pool.ray + 1;
+    f.pool.hit_uv.base = f.pool.surf;
+    f.pool.throughput_pdf.base = f.pool.surf + 1;
+    f.pool.hit_geom_id.base = reinterpret_cast<int*>(f.pool.meta) + 0;
+    f.pool.material_id.base = reinterpret_cast<int*>(f.pool.meta) + 1;
+    f.pool.remaining_bounces.base = reinterpret_cast<int*>(f.pool.meta) + 2;
+    f.pool.rng_state.base = reinterpret_cast<uint32_t*>(f.pool.meta) + 3;
     TRY(dev_alloc(r, f.shadow.ray_ori_tmax, nee_factor * P));
     TRY(dev_alloc(r, f.shadow.ray_dir, nee_factor * P));
     TRY(dev_alloc(r, f.shadow.radiance, nee_factor * P));
@@ -420,8 +423,9 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     TRYCU(cudaMemsetAsync(f.direct, 0, nee_factor * 3 * P * sizeof(float), r->stream));
     TRYCU(cudaMemsetAsync(f.indirect, 0, 3 * P * sizeof(float), r->stream));
     // InitPathPoolKernel (src/pathtrace_wavefront.cu:183-190): every slot starts dead
-    TRYCU(cudaMemsetAsync(f.pool.remaining_bounces, 0xff, P * sizeof(int), r->stream));
-    TRYCU(cudaMemsetAsync(f.pool.hit_geom_id, 0xff, P * sizeof(int), r->stream));
+    TRYCU(cudaMemsetAsync(f.pool.meta, 0xff, P * sizeof(int4), r->stream));   // remaining_bounces = hit_geom_id = -1
+    TRYCU(cudaMemsetAsync(f.pool.ray, 0, 2 * P * sizeof(float4), r->stream));
+    TRYCU(cudaMemsetAsync(f.pool.surf, 0, 2 * P * sizeof(float4), r->stream));
 
     // ---- first-bounce G-buffer (initSVGF buffers, src/wavefront_internal.cu:286-300), on request
     f.view_proj = nullptr;
@@ -909,17 +913,18 @@ int ptb_get_shadow_queue(ptb_renderer* r, float* ori_tmax4, float* dir4, float* 
 int ptb_get_path_field(ptb_renderer* r, int32_t field, void* dst, size_t bytes) {
     if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_path_field: null argument");
     CU(cudaSetDevice(r->device));
-    const void* src;
-    size_t elem;
+    const char* src;
+    size_t elem, pitch;           // element size and the stride between consecutive slots (interleaved records, common.cuh)
+    const PathPool& pool = r->frame.pool;
     switch (field) {
-        case PTB_PF_RAY_ORI: src = r->frame.pool.ray_ori; elem = 16; break;
-        case PTB_PF_RAY_DIR_DIST: src = r->frame.pool.ray_dir_dist; elem = 16; break;
-        case PTB_PF_HIT_UV: src = r->frame.pool.hit_uv; elem = 16; break;
-        case PTB_PF_THROUGHPUT_PDF: src = r->frame.pool.throughput_pdf; elem = 16; break;
-        case PTB_PF_HIT_GEOM_ID: src = r->frame.pool.hit_geom_id; elem = 4; break;
-        case PTB_PF_MATERIAL_ID: src = r->frame.pool.material_id; elem = 4; break;
-        case PTB_PF_REMAINING_BOUNCES: src = r->frame.pool.remaining_bounces; elem = 4; break;
-        case PTB_PF_RNG_STATE: src = r->frame.pool.rng_state; elem = 4; break;
+        case PTB_PF_RAY_ORI: src = (const char*)pool.ray; elem = 16; pitch = 32; break;
+        case PTB_PF_RAY_DIR_DIST: src = (const char*)(pool.ray + 1); elem = 16; pitch = 32; break;
+        case PTB_PF_HIT_UV: src = (const char*)pool.surf; elem = 16; pitch = 32; break;
+        case PTB_PF_THROUGHPUT_PDF: src = (const char*)(pool.surf + 1); elem = 16; pitch = 32; break;
+        case PTB_PF_HIT_GEOM_ID: src = (const char*)pool.meta + 0; elem = 4; pitch = 16; break;
+        case PTB_PF_MATERIAL_ID: src = (const char*)pool.meta + 4; elem = 4; pitch = 16; break;
+        case PTB_PF_REMAINING_BOUNCES: src = (const char*)pool.meta + 8; elem = 4; pitch = 16; break;
+        case PTB_PF_RNG_STATE: src = (const char*)pool.meta + 12; elem = 4; pitch = 16; break;
         default: return fail(PTB_ERR_INVALID, "ptb_get_path_field: unknown field");
     }
     const TileMap& tm = r->frame.tile;
@@ -927,11 +932,11 @@ int ptb_get_path_field(ptb_renderer* r, int32_t field, void* dst, size_t bytes) 
     if (bytes < full) return fail(PTB_ERR_INVALID, "ptb_get_path_field: buffer smaller than width*height elements");
     CU(cudaStreamSynchronize(r->stream));
     if (tm.world <= 1) {
-        CU(cudaMemcpy(dst, src, full, cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy2D(dst, elem, src, pitch, elem, (size_t)tm.owned_pixels, cudaMemcpyDeviceToHost));
         return PTB_OK;
     }
     std::vector<char> tmp((size_t)tm.owned_pixels * elem);
-    CU(cudaMemcpy(tmp.data(), src, tmp.size(), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy2D(tmp.data(), elem, src, pitch, elem, (size_t)tm.owned_pixels, cudaMemcpyDeviceToHost));
     for (int i = 0; i < tm.owned_pixels; i++)
         memcpy((char*)dst + (size_t)tm.global_pixel(i) * elem, tmp.data() + (size_t)i * elem, elem);
     return PTB_OK;
