@@ -187,6 +187,11 @@ struct PoolI {                   // one 32-bit component of the int4 `meta` reco
     T* base;
     __device__ __forceinline__ T& operator[](int i) const { return base[4 * (size_t)i]; }
 };
+// One 32-byte store for a whole (ray_ori, ray_dir_dist) record (sm_100 STG.256): a full sector, no partial write.
+__device__ __forceinline__ void stg256(float4* p, float4 a, float4 b) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+}
 struct PathPool {
     PoolF4 ray_ori;
     PoolF4 ray_dir_dist;

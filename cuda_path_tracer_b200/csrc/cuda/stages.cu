@@ -52,8 +52,7 @@ __global__ void __launch_bounds__(kThreads) k_raygen(FrameDev f) {
     Vec3 dir = normalize3(view
         + right * f.cam.pixel_length[0] * ((float)x + jx - (float)f.cam.res_x * 0.5f)
         - up * f.cam.pixel_length[1] * ((float)y + jy - (float)f.cam.res_y * 0.5f));
-    f.pool.ray_ori[slot] = make_float4(f.cam.pos[0], f.cam.pos[1], f.cam.pos[2], 0.0f);
-    f.pool.ray_dir_dist[slot] = make_float4(dir.x, dir.y, dir.z, FLT_MAX);
+    stg256(f.pool.ray + 2 * (size_t)slot, make_float4(f.cam.pos[0], f.cam.pos[1], f.cam.pos[2], 0.0f), make_float4(dir.x, dir.y, dir.z, FLT_MAX));
     f.pool.hit_geom_id[slot] = -1;
     f.pool.material_id[slot] = -1;
     f.pool.throughput_pdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
@@ -206,8 +205,9 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
         }
         if (alive) {
             f.pool.throughput_pdf[idx] = make_float4(throughput.x, throughput.y, throughput.z, next_pdf);
-            f.pool.ray_ori[idx] = make_float4(P.x + bias_n.x * PTB_EPSILON, P.y + bias_n.y * PTB_EPSILON, P.z + bias_n.z * PTB_EPSILON, 0.0f);
-            f.pool.ray_dir_dist[idx] = make_float4(next_dir.x, next_dir.y, next_dir.z, FLT_MAX);
+            stg256(f.pool.ray + 2 * (size_t)idx,
+                   make_float4(P.x + bias_n.x * PTB_EPSILON, P.y + bias_n.y * PTB_EPSILON, P.z + bias_n.z * PTB_EPSILON, 0.0f),
+                   make_float4(next_dir.x, next_dir.y, next_dir.z, FLT_MAX));
             f.pool.remaining_bounces[idx] -= 1;
             out.push_ext = true;
         } else {
