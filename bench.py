@@ -126,15 +126,31 @@ def roofline_and_cpu(r, scene, n_gpus, rank, stats_rays_per_path):
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (burst copy)"
     else:
         peak, peak_src = 7700.0, "fallback nominal HBM3e figure (MEASURED_PEAKS.json absent)"
-    traffic = None
+    traffic = issue = None
     tpath = os.path.join(ROOT, "profiles", "raycast_traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        prof = json.load(open(tpath))
+        traffic = prof.get("dram_bytes_per_launch")
+        wi = prof.get("warp_instructions_per_launch")
+        if wi and len(wi) == depth:
+            # What actually bounds the kernel: issue slots.  Warp-instructions per launch from the committed ncu
+            # capture of the same frame (deterministic: same scene, same rays) over the launch times measured live above.
+            sms, ghz = 148, 1.965
+            try:
+                import torch
+                sms = torch.cuda.get_device_properties(0).multi_processor_count
+            except Exception:  # noqa: BLE001
+                pass
+            ach = sum(wi) / (tot_ms * 1e-3) / 1e9
+            pk = sms * 4 * ghz
+            issue = {"bound": "issue slots", "unit": "G warp-instructions/s (peak = SMs x 4 schedulers x 1.965 GHz)", "achieved": round(ach, 1), "peak": round(pk, 1),
+                     "frac": round(ach / pk, 3), "warp_instructions_per_step": int(sum(wi)), "source": prof.get("warp_instructions_source")}
     achieved = tot_bytes / (tot_ms * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": "k_trace_extension", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5),
             "traffic": traffic, "peak_source": peak_src, "launches_per_step": depth, "avg_launch_ms": round(tot_ms / depth, 4),
             "algorithmic_bytes_per_launch": round(tot_bytes / depth), "mrays_per_s": round(tot_rays / (tot_ms * 1e-3) / 1e6, 1), "per_bounce": per_bounce,
-            "note": "BVH (19 MB) is L2-resident at this size: the kernel is latency/divergence-bound, the HBM figure counts ray-state streaming only"}
+            "note": "BVH (19 MB) is L2-resident at this size: the kernel is bound by issue slots under divergence (see `issue`), the HBM figure counts ray-state streaming only",
+            "issue": issue}
     cpu = None
     if sample is not None:
         import _oracle as orc
