@@ -87,10 +87,10 @@ def reference_arm(args, rank):
                         capture_output=True, text=True, timeout=3000)
     lm = [l for l in pm.stdout.splitlines() if l.startswith("REFBENCH")]
     mega = json.loads(lm[0][len("REFBENCH "):]) if lm else None
-    print(json.dumps({"impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+    print(json.dumps({"impl": "reference", "metric": "Mpaths/s", "value": v, "unit": "Mpaths/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                       "ms_per_step": rb["ms_per_frame"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                       "config": {"workload": WORKLOAD, "reference": "s64zxu/CUDA-Path-Tracer wavefront build recompiled -arch=sm_100 (oracle/Makefile), Pathtrace(NULL,0,iter) loop, wall clock around the loop",
-                                 "mrays_per_s": rb["mrays_per_s"],
+                                 "mrays_per_s": rb["mrays_per_s"], "gpus_used": 1,
                                  "megakernel_path": None if mega is None else {"ms_per_frame": mega["ms_per_frame"], "mpaths_per_s": mega["mpaths_per_s"], "mrays_per_s": mega["mrays_per_s"]}},
                       "cpu_baseline": {"value": v, "unit": "Mpaths/s", "cores": 0, "kind": "reference",
                                        "sample": "the reference has no CPU implementation of this path (SURVEY.md fact 2): this arm is its own CUDA build on one B200; the CPU port is timed in the main arm"},
