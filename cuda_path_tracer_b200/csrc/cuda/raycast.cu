@@ -9,7 +9,9 @@
 
 namespace ptb {
 
+#ifndef PTB_SH_MINBLOCKS
 #define PTB_SH_MINBLOCKS 12   /* any-hit keeps no hit record: 40 registers without spills, 48 resident warps per SM */
+#endif
 #ifndef PTB_RC_MINBLOCKS
 #define PTB_RC_MINBLOCKS 10
 #endif

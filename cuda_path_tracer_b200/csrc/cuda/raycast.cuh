@@ -23,7 +23,9 @@ static __device__ unsigned long long g_wide_dbg[8];
 #define PTB_NODE_NONE 0x7fffffff
 #define PTB_EXT_STACK 32          /* src/kernels/ray_cast.cu:35,106 */
 #define PTB_SHADOW_STACK 64
+#ifndef PTB_RC_THREADS
 #define PTB_RC_THREADS 128
+#endif
 
 // BoudingboxIntersetionTest, src/intersections.cu:34-61 (FADD, FMUL, min/max chain; no FMA).
 __device__ __forceinline__ float slab_test(float4 mn, float4 mx, Vec3 o, Vec3 inv) {
