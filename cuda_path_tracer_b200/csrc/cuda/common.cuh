@@ -144,10 +144,9 @@ struct LbvhRef {
 // three vertices inline in a 64-byte record as well (two sectors, 32-byte aligned), which removes
 // the primitive_indices -> indices_matid -> pos chain (:55-63).  RayCast is bound by the L1 data
 // pipe (wavefronts), not by bytes, so records are laid out per sector, not packed.
-//   node[4*i+0] = (left.min.xyz , bits(left link))     link >= 0 : internal node index
-//   node[4*i+1] = (left.max.xyz , bits(right link))    link <  0 : ~(sorted leaf position)
-//   node[4*i+2] = (right.min.xyz, 0)
-//   node[4*i+3] = (right.max.xyz, 0)
+//   node[4*i+0] = (lmin.x, lmin.y, lmax.x, lmax.y)     node[4*i+1] = (rmin.x, rmin.y, rmax.x, rmax.y)
+//   node[4*i+2] = (lmin.z, lmax.z, rmin.z, rmax.z)     node[4*i+3] = (bits(left link), bits(right link), 0, 0)
+//   link >= 0 : internal node index, link < 0 : ~(sorted leaf position); pairs as node_test() (raycast.cuh) consumes them
 //   tri[4*k+0]  = (v0.xyz, bits(triangle index)), tri[4*k+1] = (v1.xyz, bits(material id)),
 //   tri[4*k+2]  = (v2.xyz, 0),                    tri[4*k+3] = 0
 #define PTB_TRI_STRIDE 4
@@ -159,7 +158,12 @@ struct BvhDev {
     // 4-wide collapse of the same tree with 15-bit boxes (wide.cuh); wcell = (root_max - root_min) / PTB_WIDE_GRID
     const uint4* wnode;
     float wcell[3];
+    // the binary tree itself with both children's boxes on the same 15-bit grid: ONE 32-byte sector per node visit
+    //   bnode[2*i+0] = (x_left, x_right, y_left, y_right)   each word lo | hi << 16 (15-bit steps, rounded outwards)
+    //   bnode[2*i+1] = (z_left, z_right, left link, right link)
+    const uint4* bnode;
 };
+#define PTB_EXT_STACK_DEPTH 32       /* entries the reference's closest-hit walk stacks before it gives up (src/kernels/ray_cast.cu:35,106) */
 #define PTB_WIDE_GRID 32760.0f      /* quantisation steps across the scene box; +-2 steps of margin stay below 2^15 */
 #define PTB_WIDE_EMPTY 0x7fffffff   /* link of an unused child slot */
 

@@ -361,10 +361,10 @@ __global__ void __launch_bounds__(256) k_pack(LbvhBuffers b, const float4* __res
         int rlink = ch.y < 0 ? ~(rc - n) : rc;
         float4 lmin = b.ref.aabb_min[lc], lmax = b.ref.aabb_max[lc];
         float4 rmin = b.ref.aabb_min[rc], rmax = b.ref.aabb_max[rc];
-        b.node[4 * (size_t)i + 0] = make_float4(lmin.x, lmin.y, lmin.z, __int_as_float(llink));
-        b.node[4 * (size_t)i + 1] = make_float4(lmax.x, lmax.y, lmax.z, __int_as_float(rlink));
-        b.node[4 * (size_t)i + 2] = make_float4(rmin.x, rmin.y, rmin.z, 0.0f);
-        b.node[4 * (size_t)i + 3] = make_float4(rmax.x, rmax.y, rmax.z, 0.0f);
+        b.node[4 * (size_t)i + 0] = make_float4(lmin.x, lmin.y, lmax.x, lmax.y);     // layout of node_test(), raycast.cuh
+        b.node[4 * (size_t)i + 1] = make_float4(rmin.x, rmin.y, rmax.x, rmax.y);
+        b.node[4 * (size_t)i + 2] = make_float4(lmin.z, lmax.z, rmin.z, rmax.z);
+        b.node[4 * (size_t)i + 3] = make_float4(__int_as_float(llink), __int_as_float(rlink), 0.0f, 0.0f);
     }
     if (i < n) {
         int prim = b.ref.primitive_indices[n + i];
@@ -441,6 +441,38 @@ __global__ void __launch_bounds__(256) k_pack_wide(LbvhBuffers b) {
     out[3] = make_uint4((unsigned)link[0], (unsigned)link[1], (unsigned)link[2], (unsigned)link[3]);
 }
 
+// 32-byte binary traversal nodes (BvhDev::bnode, wide.cuh trace_closest_bq): node i keeps the LBVH's two children, their
+// boxes on the 15-bit grid of k_pack_wide (same quantiser, same outward rounding and margin).  A node visit is one
+// 32-byte sector instead of the two of the fp32 record: RayCast is co-limited by L1 wavefronts.
+__device__ __forceinline__ void quantise_box(float4 mn, float4 mx, const float org[3], const float cell[3], unsigned int q[3]) {
+    const float vmin[3] = {mn.x, mn.y, mn.z}, vmax[3] = {mx.x, mx.y, mx.z};
+    for (int a = 0; a < 3; a++) {
+        float inv_cell = cell[a] > 0.0f ? 1.0f / cell[a] : 0.0f;
+        float ql = floorf((vmin[a] - org[a]) * inv_cell) - 2.0f;
+        float qh = ceilf((vmax[a] - org[a]) * inv_cell) + 2.0f;
+        unsigned int lo = (unsigned int)fminf(fmaxf(ql, 0.0f), 32767.0f);
+        unsigned int hi = (unsigned int)fminf(fmaxf(qh, 0.0f), 32767.0f);
+        q[a] = lo | (hi << 16);
+    }
+}
+__global__ void __launch_bounds__(256) k_pack_bq(LbvhBuffers b) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = b.num_triangles;
+    if (i >= n - 1) return;
+    int2 ch = b.ref.child_nodes[i];
+    int lc = decode_node(ch.x), rc = decode_node(ch.y);
+    int llink = ch.x < 0 ? ~(lc - n) : lc;
+    int rlink = ch.y < 0 ? ~(rc - n) : rc;
+    const float4 wmin = b.ref.aabb_min[0], wmax = b.ref.aabb_max[0];
+    const float cell[3] = {__fdiv_rn(wmax.x - wmin.x, PTB_WIDE_GRID), __fdiv_rn(wmax.y - wmin.y, PTB_WIDE_GRID), __fdiv_rn(wmax.z - wmin.z, PTB_WIDE_GRID)};
+    const float org[3] = {wmin.x, wmin.y, wmin.z};
+    unsigned int ql[3], qr[3];
+    quantise_box(b.ref.aabb_min[lc], b.ref.aabb_max[lc], org, cell, ql);
+    quantise_box(b.ref.aabb_min[rc], b.ref.aabb_max[rc], org, cell, qr);
+    b.bnode[2 * (size_t)i + 0] = make_uint4(ql[0], qr[0], ql[1], qr[1]);
+    b.bnode[2 * (size_t)i + 1] = make_uint4(ql[2], qr[2], (unsigned)llink, (unsigned)rlink);
+}
+
 // ---- host side -------------------------------------------------------------------------------
 template <typename T>
 static cudaError_t dalloc(T*& p, size_t count, size_t& total) {
@@ -469,6 +501,7 @@ int lbvh_alloc(LbvhBuffers& b, int n) {
     A(dalloc(b.node, 4 * (size_t)n, t));
     A(dalloc(b.tri, PTB_TRI_STRIDE * (size_t)n, t));
     A(dalloc(b.wnode, 4 * (size_t)n, t));
+    A(dalloc(b.bnode, 2 * (size_t)n, t));
     A(dalloc(b.key_a, (size_t)n, t));
     A(dalloc(b.key_b, (size_t)n, t));
     A(dalloc(b.val_b, (size_t)n, t));
@@ -484,7 +517,7 @@ int lbvh_alloc(LbvhBuffers& b, int n) {
 
 void lbvh_free(LbvhBuffers& b) {
     void* ptrs[] = {b.ref.aabb_min, b.ref.aabb_max, b.ref.centroid, b.ref.primitive_indices, b.ref.morton_codes,
-                    b.ref.child_nodes, b.ref.parent, b.ref.escape_indices, b.ref.world_aabb, b.node, b.tri, b.wnode,
+                    b.ref.child_nodes, b.ref.parent, b.ref.escape_indices, b.ref.world_aabb, b.node, b.tri, b.wnode, b.bnode,
                     b.key_a, b.key_b, b.val_b, b.counts, b.totals, b.flags, b.world_enc, b.max_depth};
     for (void* p : ptrs) if (p) cudaFree(p);
     b = LbvhBuffers{};
@@ -516,6 +549,7 @@ int lbvh_build(LbvhBuffers& b, const float4* pos, const int4* indices_matid, cud
     k_escape_depth<<<nb, bs, 0, s>>>(b); count++;
     k_pack<<<nb, bs, 0, s>>>(b, pos, indices_matid); count++;
     k_pack_wide<<<nb, bs, 0, s>>>(b); count++;
+    k_pack_bq<<<nb, bs, 0, s>>>(b); count++;
     if (launches) *launches += count;
     return (int)cudaGetLastError();
 }

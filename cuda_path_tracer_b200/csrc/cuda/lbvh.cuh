@@ -12,6 +12,7 @@ struct LbvhBuffers {
     float4* node = nullptr;      // 4 * (N-1)
     float4* tri = nullptr;       // PTB_TRI_STRIDE * N
     uint4* wnode = nullptr;      // 4 * (N-1): 4-wide quantised nodes (BvhDev::wnode), indexed by the binary node they collapse
+    uint4* bnode = nullptr;      // 2 * (N-1): 32-byte binary nodes with 15-bit boxes (BvhDev::bnode)
     // scratch kept for rebuilds
     unsigned int* key_a = nullptr;   // 30-bit Morton codes, ping
     unsigned int* key_b = nullptr;   // pong

@@ -60,12 +60,9 @@ __device__ __forceinline__ Hit mega_closest(const BvhDev& bvh, Vec3 o, Vec3 d, i
             }
             node = PTB_NODE_NONE;
         } else {
-            const float4* np = bvh.node + 4 * (size_t)node;
-            F8 nl = ldg256(np), nr = ldg256(np + 2);
-            float4 n0 = nl.a, n1 = nl.b, n2 = nr.a, n3 = nr.b;
-            float t_l = slab_test(n0, n1, o, inv);
-            float t_r = slab_test(n2, n3, o, inv);
-            int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
+            const NodePair nt = node_test(bvh.node + 4 * (size_t)node, o, inv);
+            const float t_l = nt.t_l, t_r = nt.t_r;
+            const int left = nt.left, right = nt.right;
             bool hit_l = (t_l != -1.0f && t_l < h.t);
             bool hit_r = (t_r != -1.0f && t_r < h.t);
             if (hit_l && hit_r) {

@@ -58,8 +58,88 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_exte
     }
 }
 
-// (A persistent-lane scheduler -- a warp owns a chunk of the queue and refills lanes whose ray ended -- was measured
-// 1.3-1.4x slower than one 32-ray batch per warp fetch and is no longer part of the build)
+// ---- persistent lanes -----------------------------------------------------------------------------------------------
+// A warp keeps walking while lanes finish; once `refill` lanes have nothing to do it retires their rays (write-back + Logic)
+// and hands them the next queue entries.  refill == 32 degenerates to one batch per fetch.  The loop has ONE back edge and
+// every decision that shapes it is warp-uniform (ballots at the two converged points), so the lanes of a warp reconverge
+// after every traversal step whatever their rays do.
+struct StackShared {                         // the whole column in shared memory
+    static constexpr int kShared = PTB_EXT_STACK;
+    int* col;
+    __device__ __forceinline__ explicit StackShared(int* c) : col(c) {}
+    __device__ __forceinline__ int get(int i) const { return col[i * PTB_RC_THREADS]; }
+    __device__ __forceinline__ void set(int i, int v) { col[i * PTB_RC_THREADS] = v; }
+};
+template <int SH>
+struct StackHybrid {                         // the SH entries nearest the root in shared memory, deeper ones in local memory
+    static constexpr int kShared = SH;
+    int* col;
+    int loc[PTB_EXT_STACK - SH];
+    __device__ __forceinline__ explicit StackHybrid(int* c) : col(c) {}
+    __device__ __forceinline__ int get(int i) const { return i < SH ? col[i * PTB_RC_THREADS] : loc[i - SH]; }
+    __device__ __forceinline__ void set(int i, int v) { if (i < SH) col[i * PTB_RC_THREADS] = v; else loc[i - SH] = v; }
+};
+
+template <bool FUSE_LOGIC, class WALK, class STACK, int MINB, int STEPS = 1>
+__global__ void __launch_bounds__(PTB_RC_THREADS, MINB) k_trace_extension_pl(FrameDev f, int bounce, int* cursor, int refill) {
+    __shared__ int stack[STACK::kShared * PTB_RC_THREADS];
+    int* ctr = f.ctr + bounce * CTR_STRIDE;
+    const int count = ctr[CTR_EXT];
+    STACK st(stack + threadIdx.x);
+    const unsigned lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    int path = -1;
+    Vec3 dir;
+    WALK w;
+    w.reset();
+    bool exhausted = false;
+    for (;;) {
+        // ---- converged: hand out queue entries
+        const unsigned idle_mask = __ballot_sync(0xffffffffu, path < 0);
+        const int n_idle = __popc(idle_mask);
+        if (exhausted && n_idle == 32) break;
+        if (!exhausted && n_idle >= refill) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(cursor, n_idle);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            exhausted = base + n_idle >= count;
+            const int i = base + __popc(idle_mask & lt);
+            if (path < 0 && i < count) {
+                path = __ldg(&f.q_ext[i]);
+                float4 o4 = f.pool.ray_ori[path];
+                float4 d4 = f.pool.ray_dir_dist[path];
+                dir = Vec3(d4.x, d4.y, d4.z);
+                w.init(f.bvh, Vec3(o4.x, o4.y, o4.z), dir);
+            }
+        }
+        // ---- walk until enough lanes are out of work
+        const int want = exhausted ? 32 : refill;
+        int n_done;
+        do {
+#pragma unroll
+            for (int k = 0; k < STEPS; k++)
+                if (w.busy()) w.step(f.bvh, st);
+            n_done = __popc(__ballot_sync(0xffffffffu, !w.busy()));
+        } while (n_done < want);
+        // ---- converged: retire finished rays (write-back, src/kernels/ray_cast.cu:111-121, then Logic)
+        const bool fin = path >= 0 && !w.busy();
+        int queue = -1;
+        if (fin) {
+            Hit h = w.finish(f.bvh, st);
+            if (h.prim == -1) {
+                f.pool.ray_dir_dist[path].w = -1.0f;
+                f.pool.hit_geom_id[path] = -1;
+            } else {
+                f.pool.ray_dir_dist[path].w = h.t;
+                f.pool.material_id[path] = h.mat;
+                f.pool.hit_geom_id[path] = h.prim;
+                f.pool.hit_uv[path] = make_float4(h.u, h.v, 0.0f, 0.0f);
+            }
+            if (FUSE_LOGIC) queue = logic_path<true>(f, path, h.prim, h.mat, make_float4(dir.x, dir.y, dir.z, h.t));
+        }
+        if (FUSE_LOGIC) logic_dispatch(f, ctr, queue, path);
+        if (fin) path = -1;
+    }
+}
 
 template <int STACK, bool SHARED, bool WIDE>
 __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_SH_MINBLOCKS : 1) k_trace_shadow(FrameDev f, int bounce) {
@@ -91,7 +171,30 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_
 
 static inline int rc_grid(const LaunchCfg& c) { return c.num_sms * (c.rc_blocks > 0 ? c.rc_blocks : 8); }
 
-static void run_extension(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s, bool fuse_logic = false) {
+template <class WALK, class STACK, int MINB, int STEPS = 1>
+static void run_extension_pl(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s, bool fuse_logic) {
+    const int refill = c.rc_refill < 1 ? 32 : c.rc_refill > 32 ? 32 : c.rc_refill;
+    const int grid = c.num_sms * MINB;
+    if (fuse_logic) k_trace_extension_pl<true, WALK, STACK, MINB, STEPS><<<grid, PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, refill);
+    else k_trace_extension_pl<false, WALK, STACK, MINB, STEPS><<<grid, PTB_RC_THREADS, 0, s>>>(f, bounce, cursor, refill);
+}
+
+static void run_extension(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c_in, cudaStream_t s, bool fuse_logic = false) {
+    LaunchCfg c = c_in;
+    if (bounce == 0 && !c.rc_b0) c.rc_mode = 0;      // primary rays are coherent and of equal length: one batch per fetch is the best schedule
+    // rc_mode: 0 = one batch per fetch on the fp32 records (below); 1 = persistent lanes, fp32 records; 2 = persistent lanes,
+    // 32-byte quantised records.  rc_stack: 1 = hybrid stack (8 entries in shared memory, the rest local).  rc_minb: resident
+    // blocks per SM the kernel is built and launched for (10: 48 registers, 9: 56, 8: 64).
+    if (c.rc_mode == 1 && c.rc_steps == 2) return run_extension_pl<WalkBinary, StackShared, 10, 2>(f, bounce, cursor, c, s, fuse_logic);
+    if (c.rc_mode == 1 && c.rc_steps == 4) return run_extension_pl<WalkBinary, StackShared, 10, 4>(f, bounce, cursor, c, s, fuse_logic);
+    if (c.rc_mode == 1 || c.rc_mode == 2) {
+#define PTB_PL(W, S, B) return run_extension_pl<W, S, B>(f, bounce, cursor, c, s, fuse_logic)
+#define PTB_PL_B(W, S) do { if (c.rc_minb == 8) PTB_PL(W, S, 8); if (c.rc_minb == 9) PTB_PL(W, S, 9); PTB_PL(W, S, 10); } while (0)
+        if (c.rc_mode == 1) { if (c.rc_stack) PTB_PL_B(WalkBinary, StackHybrid<8>); else PTB_PL_B(WalkBinary, StackShared); }
+        else { if (c.rc_stack) PTB_PL_B(WalkBq, StackHybrid<8>); else PTB_PL_B(WalkBq, StackShared); }
+#undef PTB_PL_B
+#undef PTB_PL
+    }
     const bool wide = (c.wide & 2) != 0;
     if (fuse_logic && wide) k_trace_extension<true, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
     else if (fuse_logic) k_trace_extension<true, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);

@@ -5,7 +5,7 @@
 // walk stops when 32 entries are stacked.  With identical slab / triangle arithmetic this makes
 // the winning triangle, t and (u, v) bit-identical, including for equal-t ties on shared edges.
 // What changes is the memory side: one 64-byte node record per internal node (2 x LDG.256,
-// instead of int2 + 4 scattered float4), vertices inline in the leaf (LDG.256 + LDG.128,
+// instead of int2 + 4 scattered float4; tested with two-wide fp32 instructions, node_test()), vertices inline in the leaf (LDG.256 + LDG.128,
 // instead of primitive_indices -> indices_matid -> 3 x pos), the stack in shared memory instead of
 // local memory, and no function calls (the reference's two tests are __noinline__).
 #pragma once
@@ -75,6 +75,47 @@ __device__ __forceinline__ F8 ldg256(const float4* p) {
     return r;
 }
 
+// ---- one internal node = both children's slab tests, on sm_100's two-wide fp32 instructions -----------------------------
+// RayCast is bound by issue slots, and 24 of the ~67 instructions of a node visit are the `(plane -
+// origin) * inv` of twelve planes.  sub.rn.f32x2 / mul.rn.f32x2 (FADD2 / FMUL2) do two of them per issue slot with the same
+// per-element IEEE rounding, so the result is bit for bit slab_test()'s.  The node record is laid out for it:
+//   node[4*i+0] = (lmin.x, lmin.y, lmax.x, lmax.y)     node[4*i+1] = (rmin.x, rmin.y, rmax.x, rmax.y)
+//   node[4*i+2] = (lmin.z, lmax.z, rmin.z, rmax.z)     node[4*i+3] = (bits(left link), bits(right link), 0, 0)
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+struct U64x4 { u64 a, b, c, d; };
+__device__ __forceinline__ U64x4 ldg256_b64(const void* p) {
+    U64x4 r;
+    asm("ld.global.nc.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(r.a), "=l"(r.b), "=l"(r.c), "=l"(r.d) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ float slab_result(float t1x, float t2x, float t1y, float t2y, float t1z, float t2z) {
+    float t_near = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
+    float t_far = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
+    if (t_near <= t_far && t_far > 0.0f) return fmaxf(0.0f, t_near);
+    return -1.0f;
+}
+struct NodePair { float t_l, t_r; int left, right; };    // slab_test() of either child (-1: missed) and the two links
+__device__ __forceinline__ NodePair node_test(const float4* np, Vec3 o, Vec3 inv) {
+    const u64 oxy = pack2(o.x, o.y), ixy = pack2(inv.x, inv.y), ozz = pack2(o.z, o.z), izz = pack2(inv.z, inv.z);
+    const U64x4 q = ldg256_b64(np), z = ldg256_b64(np + 2);
+    const u64 A = mul2(sub2(q.a, oxy), ixy), B = mul2(sub2(q.b, oxy), ixy);     // left:  (t1x, t1y), (t2x, t2y)
+    const u64 C = mul2(sub2(q.c, oxy), ixy), D = mul2(sub2(q.d, oxy), ixy);     // right
+    const u64 E = mul2(sub2(z.a, ozz), izz), F = mul2(sub2(z.b, ozz), izz);     // (t1z, t2z) left, right
+    float t1x, t1y, t2x, t2y, t1z, t2z, fl, fr;
+    NodePair r;
+    unpack2(A, t1x, t1y); unpack2(B, t2x, t2y); unpack2(E, t1z, t2z);
+    r.t_l = slab_result(t1x, t2x, t1y, t2y, t1z, t2z);
+    unpack2(C, t1x, t1y); unpack2(D, t2x, t2y); unpack2(F, t1z, t2z);
+    r.t_r = slab_result(t1x, t2x, t1y, t2y, t1z, t2z);
+    unpack2(z.c, fl, fr);
+    r.left = __float_as_int(fl); r.right = __float_as_int(fr);
+    return r;
+}
+
 struct Hit {
     int prim;      // triangle index, -1 = miss
     int mat;       // material id of the hit triangle
@@ -106,12 +147,9 @@ __device__ __forceinline__ Hit trace_closest(const BvhDev& bvh, Vec3 o, Vec3 d, 
             }
             node = PTB_NODE_NONE;
         } else {
-            const float4* np = bvh.node + 4 * (size_t)node;
-            F8 nl = ldg256(np), nr = ldg256(np + 2);
-            float4 n0 = nl.a, n1 = nl.b, n2 = nr.a, n3 = nr.b;
-            float t_l = slab_test(n0, n1, o, inv);
-            float t_r = slab_test(n2, n3, o, inv);
-            int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
+            const NodePair nt = node_test(bvh.node + 4 * (size_t)node, o, inv);
+            const float t_l = nt.t_l, t_r = nt.t_r;
+            const int left = nt.left, right = nt.right;
             bool hit_l = (t_l != -1.0f && t_l < h.t);
             bool hit_r = (t_r != -1.0f && t_r < h.t);
             if (hit_l && hit_r) {
@@ -149,12 +187,9 @@ __device__ __forceinline__ int trace_any(const BvhDev& bvh, Vec3 o, Vec3 d, floa
             if (t > PTB_EPSILON && t < t_limit) return 1;
             node = PTB_NODE_NONE;
         } else {
-            const float4* np = bvh.node + 4 * (size_t)node;
-            F8 nl = ldg256(np), nr = ldg256(np + 2);
-            float4 n0 = nl.a, n1 = nl.b, n2 = nr.a, n3 = nr.b;
-            float t_l = slab_test(n0, n1, o, inv);
-            float t_r = slab_test(n2, n3, o, inv);
-            int left = __float_as_int(n0.w), right = __float_as_int(n1.w);
+            const NodePair nt = node_test(bvh.node + 4 * (size_t)node, o, inv);
+            const float t_l = nt.t_l, t_r = nt.t_r;
+            const int left = nt.left, right = nt.right;
             bool hit_l = (t_l != -1.0f && tmax > t_l);
             bool hit_r = (t_r != -1.0f && tmax > t_r);
             if (hit_l && hit_r) {

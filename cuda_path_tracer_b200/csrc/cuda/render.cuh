@@ -65,6 +65,9 @@ struct LaunchCfg {
     int overlap_shadow;       // frame graph: TraceShadow(b) runs beside TraceExtension(b) on a forked branch
     int wide;                 // 4-wide quantised traversal (wide.cuh): bit 0 shadow rays, bit 1 extension rays, bit 2 megakernel
     int sh_blocks;            // resident blocks per SM of the wide shadow kernel
+    int rc_mode;              // extension-ray scheduler / node format (raycast.cu run_extension)
+    int rc_stack, rc_minb, rc_steps, rc_b0;    // see raycast.cu run_extension
+    int rc_refill;            // persistent lanes: idle lanes per warp that trigger a refill (32 = one batch per fetch)
     int mega_regen;           // megakernel: a lane whose path ended takes the next pixel at once (path regeneration)
     int mega_refill;          // megakernel: regenerate once this many lanes of a warp are idle
     int mega_blocks;          // megakernel: resident blocks per SM the persistent grid is sized for

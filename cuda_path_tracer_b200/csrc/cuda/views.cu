@@ -133,11 +133,9 @@ __global__ void __launch_bounds__(128) k_bvh_heatmap(BvhDev bvh, CameraDev cam, 
         if (node < 0) {
             node = PTB_NODE_NONE;
         } else {
-            const float4* np = bvh.node + 4 * (size_t)node;
-            F8 nl = ldg256(np), nr = ldg256(np + 2);
-            float t_l = slab_test(nl.a, nl.b, o, inv);
-            float t_r = slab_test(nr.a, nr.b, o, inv);
-            int left = __float_as_int(nl.a.w), rightc = __float_as_int(nl.b.w);
+            const NodePair nt = node_test(bvh.node + 4 * (size_t)node, o, inv);
+            const float t_l = nt.t_l, t_r = nt.t_r;
+            const int left = nt.left, rightc = nt.right;
             bool hit_l = (t_l != -1.0f), hit_r = (t_r != -1.0f);
             if (hit_l && hit_r) {
                 bool left_first = t_l < t_r;

@@ -202,6 +202,150 @@ __device__ __forceinline__ Hit trace_closest_wide(const BvhDev& bvh, const WideR
     return h;
 }
 
+// ---- resumable walks: one traversal step per call, so that a scheduler can interleave rays of different ages in one warp
+// (raycast.cu, persistent lanes).  STACK is a policy with get(i) / set(i, v) (raycast.cu).
+// WalkBinary is trace_closest() cut at the loop body: the reference's order, the reference's arithmetic, its 32-entry abort.
+struct WalkBinary {
+    Vec3 o, d, inv;
+    Hit h;
+    int node, sp;
+    __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
+    __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
+    __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o_, Vec3 d_) {
+        o = o_; d = d_;
+        inv = Vec3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
+        h.prim = -1; h.mat = -1; h.t = FLT_MAX; h.u = 0.0f; h.v = 0.0f;
+        sp = 0;
+        node = (slab_test(bvh.root_min, bvh.root_max, o, inv) == -1.0f) ? PTB_NODE_NONE : 0;
+    }
+    template <class STACK>
+    __device__ __forceinline__ void step(const BvhDev& bvh, STACK& st) {
+        if (node == PTB_NODE_NONE) node = st.get(--sp);
+        if (node < 0) {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
+            float u, v;
+            float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, u, v);
+            if (t > PTB_EPSILON && t < h.t) {
+                h.t = t; h.u = u; h.v = v;
+                h.prim = __float_as_int(a.w);
+                h.mat = __float_as_int(b.w);
+            }
+            node = PTB_NODE_NONE;
+        } else {
+            const NodePair nt = node_test(bvh.node + 4 * (size_t)node, o, inv);
+            const float t_l = nt.t_l, t_r = nt.t_r;
+            const int left = nt.left, right = nt.right;
+            bool hit_l = (t_l != -1.0f && t_l < h.t);
+            bool hit_r = (t_r != -1.0f && t_r < h.t);
+            if (hit_l && hit_r) {
+                bool left_first = t_l < t_r;
+                st.set(sp++, left_first ? right : left);
+                node = left_first ? left : right;
+            } else if (hit_l) node = left;
+            else if (hit_r) node = right;
+            else node = PTB_NODE_NONE;
+        }
+        if (sp >= PTB_EXT_STACK) { node = PTB_NODE_NONE; sp = 0; }   // src/kernels/ray_cast.cu:106
+    }
+    template <class STACK>
+    __device__ __forceinline__ Hit finish(const BvhDev&, STACK&) { return h; }
+};
+
+// WalkBq: the same binary tree through the 32-byte quantised records (BvhDev::bnode), near child first.  Exactness as in
+// trace_closest_wide(): boxes are conservative, a hit is accepted through the reference's test on the leaf's fp32 box, and a
+// result that could depend on the reference's visiting order is re-traced in that order (finish()).
+struct WalkBq {
+    Vec3 o, d;
+    float iqx, iqy, iqz, bx, by, bz;          // t(q) = fma(32768 + q, iq, b)  (WideRay)
+    unsigned near_x, near_y, near_z;
+    float t, u, v, second;                    // best hit so far (t = FLT_MAX: none) and the nearest other accepted candidate
+    int leaf;                                 // sorted leaf position of the best hit
+    int node, sp;
+    bool bad;
+    __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
+    __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
+    __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o_, Vec3 d_) {
+        WideRay r = wide_setup(bvh, o_, d_);
+        o = o_; d = d_;
+        iqx = r.iqx; iqy = r.iqy; iqz = r.iqz; bx = r.bx; by = r.by; bz = r.bz;
+        near_x = r.near_x; near_y = r.near_y; near_z = r.near_z;
+        t = FLT_MAX; u = 0.0f; v = 0.0f; second = FLT_MAX; leaf = -1;
+        sp = 0;
+        bad = !r.ok;
+        node = bad ? PTB_NODE_NONE : 0;
+    }
+    template <class STACK>
+    __device__ __forceinline__ void step(const BvhDev& bvh, STACK& st) {
+        if (node == PTB_NODE_NONE) node = st.get(--sp);
+        const float limit = t * PTB_WIDE_SLACK;           // +inf while there is no hit
+        if (node >= 0) {
+            F8 q = ldg256(reinterpret_cast<const float4*>(bvh.bnode + 2 * (size_t)node));
+            const unsigned xl = __float_as_uint(q.a.x), xr = __float_as_uint(q.a.y), yl = __float_as_uint(q.a.z), yr = __float_as_uint(q.a.w);
+            const unsigned zl = __float_as_uint(q.b.x), zr = __float_as_uint(q.b.y);
+            const int left = __float_as_int(q.b.z), right = __float_as_int(q.b.w);
+            const unsigned far_x = near_x ^ 0x0220u, far_y = near_y ^ 0x0220u, far_z = near_z ^ 0x0220u;
+            float tn_l = fmaxf(fmaxf(fmaf(wide_plane(xl, near_x), iqx, bx), fmaf(wide_plane(yl, near_y), iqy, by)),
+                               fmaxf(fmaf(wide_plane(zl, near_z), iqz, bz), 0.0f));
+            float tf_l = fminf(fminf(fmaf(wide_plane(xl, far_x), iqx, bx), fmaf(wide_plane(yl, far_y), iqy, by)),
+                               fminf(fmaf(wide_plane(zl, far_z), iqz, bz), limit));
+            float tn_r = fmaxf(fmaxf(fmaf(wide_plane(xr, near_x), iqx, bx), fmaf(wide_plane(yr, near_y), iqy, by)),
+                               fmaxf(fmaf(wide_plane(zr, near_z), iqz, bz), 0.0f));
+            float tf_r = fminf(fminf(fmaf(wide_plane(xr, far_x), iqx, bx), fmaf(wide_plane(yr, far_y), iqy, by)),
+                               fminf(fmaf(wide_plane(zr, far_z), iqz, bz), limit));
+            const bool hit_l = tn_l <= tf_l, hit_r = tn_r <= tf_r;
+            if (hit_l && hit_r) {
+                const bool left_first = tn_l <= tn_r;
+                if (sp < PTB_WIDE_STACK) st.set(sp++, left_first ? right : left);
+                else bad = true;
+                node = left_first ? left : right;
+            } else if (hit_l) node = left;
+            else if (hit_r) node = right;
+            else node = PTB_NODE_NONE;
+        } else {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
+            float tu, tv;
+            float tt = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), o, d, tu, tv);
+            if (tt > PTB_EPSILON && tt < limit) {
+                const Vec3 inv(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));      // 1.0f / ray.direction, as the reference has it
+                float tb = leaf_box_test(a, b, c, o, inv);
+                if (tb != -1.0f && tb < limit) {
+                    if (tt < t && tb < t) {                          // the reference's acceptance, src/kernels/ray_cast.cu:68,93-94
+                        second = fminf(second, t);
+                        t = tt; u = tu; v = tv;
+                        leaf = ~node;
+                    } else {
+                        second = fminf(second, tt);
+                    }
+                }
+            }
+            node = PTB_NODE_NONE;
+        }
+        if (bad) { node = PTB_NODE_NONE; sp = 0; }
+    }
+    template <class STACK>
+    __device__ __forceinline__ Hit finish(const BvhDev& bvh, STACK& st) {
+        const bool ambiguous = bad || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
+        if (ambiguous) {     // about one ray in 10^5: the reference-order walk decides
+            WalkBinary w;
+            w.init(bvh, o, d);
+            while (w.busy()) w.step(bvh, st);
+            return w.h;
+        }
+        Hit h;
+        h.prim = -1; h.mat = -1; h.t = t; h.u = u; h.v = v;
+        if (leaf >= 0) {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)leaf;
+            h.prim = __float_as_int(__ldg(tp).w);
+            h.mat = __float_as_int(__ldg(tp + 1).w);
+        }
+        return h;
+    }
+};
+
 // The two walks behind one call: wide first, the reference-order binary walk where the wide one cannot vouch for the result.
 __device__ __forceinline__ Hit trace_closest_exact(const BvhDev& bvh, Vec3 o, Vec3 d, int* stack, int stride) {
     WideRay r = wide_setup(bvh, o, d);

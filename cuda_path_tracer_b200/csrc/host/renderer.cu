@@ -293,6 +293,12 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         r->launch.overlap_shadow = knob("PTB_OVERLAP_SHADOW", 1);
         r->launch.wide = knob("PTB_WIDE", 1);
         r->launch.sh_blocks = knob("PTB_SH_BLOCKS", 12);
+        r->launch.rc_mode = knob("PTB_RC_MODE", 0);
+        r->launch.rc_refill = knob("PTB_RC_REFILL", 32);
+        r->launch.rc_stack = knob("PTB_RC_STACK", 0);
+        r->launch.rc_minb = knob("PTB_RC_MINB", 10);
+        r->launch.rc_steps = knob("PTB_RC_STEPS", 1);
+        r->launch.rc_b0 = knob("PTB_RC_B0", 0);
         r->launch.mega_regen = knob("PTB_MEGA_REGEN", 1);
         r->launch.mega_refill = knob("PTB_MEGA_REFILL", 1);
         r->launch.mega_blocks = knob("PTB_MEGA_BLOCKS", 10);
@@ -370,6 +376,7 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         f.bvh.node = r->lbvh.node;
         f.bvh.tri = r->lbvh.tri;
         f.bvh.wnode = r->lbvh.wnode;
+        f.bvh.bnode = r->lbvh.bnode;
         // the quantisation step k_pack_wide used: (root_max - root_min) / PTB_WIDE_GRID, IEEE division on both sides
         f.bvh.wcell[0] = (root[1].x - root[0].x) / PTB_WIDE_GRID;
         f.bvh.wcell[1] = (root[1].y - root[0].y) / PTB_WIDE_GRID;
@@ -381,6 +388,10 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         // any-hit stack: at most one entry per internal node on the root-to-leaf path, i.e. <= lbvh_max_depth
         const int dmax = r->lbvh_max_depth;
         r->launch.shadow_deep = dmax <= 32 ? 0 : dmax <= 48 ? 1 : dmax <= 64 ? 2 : 3;
+        // The reference's closest-hit walk gives up once 32 entries are stacked (src/kernels/ray_cast.cu:106), which can only
+        // happen in a tree at least 32 levels deep.  The quantised walks visit in another order and would not give up at
+        // the same ray, so extension rays of such trees always take the reference-order walk on the fp32 records.
+        if (dmax >= PTB_EXT_STACK_DEPTH) { r->launch.wide &= ~2; if (r->launch.rc_mode == 2) r->launch.rc_mode = 1; }
     }
 
     // ---- path pool, queues, accumulators (initWavefrontQueues / initImageSystem,

@@ -90,6 +90,45 @@ int ptb_scene_set_environment(ptb_scene* s, const float* rgb, int32_t width, int
     return PTB_OK;
 }
 
+int ptb_scene_add_texture(ptb_scene* s, const void* pixels, int32_t width, int32_t height, int32_t format, int32_t clamp_y) {
+    if (!s || !pixels || width <= 0 || height <= 0) return fail(PTB_ERR_INVALID, "ptb_scene_add_texture: bad argument");
+    if (format < PTB_TEX_RGBA8 || format > PTB_TEX_RGBA32F) return fail(PTB_ERR_INVALID, "ptb_scene_add_texture: unknown format");
+    HostTexture t;
+    t.width = width; t.height = height; t.clamp_y = clamp_y != 0;
+    const size_t n = (size_t)width * height;
+    if (format == PTB_TEX_RGBA8) {
+        t.channels = 4; t.is_float = false;
+        t.rgba8.assign((const uint8_t*)pixels, (const uint8_t*)pixels + 4 * n);
+    } else {
+        t.channels = format == PTB_TEX_R32F ? 1 : 4; t.is_float = true;
+        t.f32.assign((const float*)pixels, (const float*)pixels + t.channels * n);
+    }
+    s->textures.push_back(std::move(t));
+    return (int)s->textures.size() - 1;
+}
+
+int ptb_scene_set_environment_table(ptb_scene* s, int32_t env_tex_id, int32_t pdf_map_id, const float* probs, const int32_t* aliases,
+                                    int32_t width, int32_t height) {
+    if (!s || !probs || !aliases || width <= 0 || height <= 0) return fail(PTB_ERR_INVALID, "ptb_scene_set_environment_table: bad argument");
+    if (s->env.width > 0) return fail(PTB_ERR_STATE, "ptb_scene_set_environment_table: environment already set");
+    const int nt = (int)s->textures.size();
+    if (env_tex_id < 0 || env_tex_id >= nt || pdf_map_id < 0 || pdf_map_id >= nt)
+        return fail(PTB_ERR_INVALID, "ptb_scene_set_environment_table: texture id out of range (add the textures first)");
+    const HostTexture& et = s->textures[env_tex_id];
+    const HostTexture& pt = s->textures[pdf_map_id];
+    if (!et.is_float || et.channels != 4 || !pt.is_float || pt.channels != 1 || et.width != width || et.height != height || pt.width != width || pt.height != height)
+        return fail(PTB_ERR_INVALID, "ptb_scene_set_environment_table: the environment must be an RGBA32F and its pdf map an R32F texture of the table's size");
+    const size_t n = (size_t)width * height;
+    for (size_t i = 0; i < n; i++)
+        if (aliases[i] < 0 || (size_t)aliases[i] >= n) return fail(PTB_ERR_INVALID, "ptb_scene_set_environment_table: alias out of range");
+    s->env.width = width; s->env.height = height;
+    s->env.env_tex_id = env_tex_id; s->env.pdf_map_id = pdf_map_id;
+    s->env.probs.assign(probs, probs + n);
+    s->env.aliases.assign(aliases, aliases + n);
+    s->env.pdf_map = pt.f32;
+    return PTB_OK;
+}
+
 int ptb_scene_set_camera(ptb_scene* s, const int32_t resolution[2], float fovy_deg, const float eye[3], const float look_at[3],
                          const float up[3], int32_t trace_depth) {
     if (!s || !resolution || !eye || !look_at || !up) return fail(PTB_ERR_INVALID, "ptb_scene_set_camera: null argument");

@@ -90,6 +90,17 @@ int ptb_scene_from_arrays(const float* pos, const float* nor, const float* uv, c
 /* Attach an equirect RGB32F environment image (what Scene::buildEnvMapAliasTable does after
  * stbi_loadf, src/scene.cpp:183-300).  rgb has 3*width*height floats, row-major. */
 int ptb_scene_set_environment(ptb_scene* s, const float* rgb, int32_t width, int32_t height);
+/* Textures and the environment of a scene built with ptb_scene_from_arrays, from images the caller already holds -- what
+ * a live reference `Scene` keeps as CUDA arrays behind Scene::texture_handles (Scene::createTexture, src/scene.h:94-145):
+ * ptb_scene_add_texture appends one image and returns its id (>= 0; ids count up in call order, as Scene::loadTexture /
+ * buildEnvMapAliasTable assign them, src/scene.cpp:58-81,283-297) or a negative status.  PTB_TEX_RGBA8: uchar4 read as
+ * normalised float; PTB_TEX_R32F / PTB_TEX_RGBA32F: float / float4 read as they are.  X wraps, Y wraps or clamps (clamp_y).
+ * ptb_scene_set_environment_table then names the two textures that are the environment and its pdf map and hands over
+ * the Vose alias table Scene::buildEnvMapAliasTable built (EnvMap::probs / aliases, src/scene.h:37-48). */
+enum { PTB_TEX_RGBA8 = 0, PTB_TEX_R32F = 1, PTB_TEX_RGBA32F = 2 };
+int ptb_scene_add_texture(ptb_scene* s, const void* pixels, int32_t width, int32_t height, int32_t format, int32_t clamp_y);
+int ptb_scene_set_environment_table(ptb_scene* s, int32_t env_tex_id, int32_t pdf_map_id, const float* probs,
+                                    const int32_t* aliases, int32_t width, int32_t height);
 /* Recompute camera.view/right/up/fov/pixel_length from eye/lookat/up/fovy/resolution
  * (src/scene.cpp:560-572) and store it in the scene. */
 int ptb_scene_set_camera(ptb_scene* s, const int32_t resolution[2], float fovy_deg,
