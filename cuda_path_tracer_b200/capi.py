@@ -62,6 +62,18 @@ class TileInfo(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("width", "height", "owned_pixels", "rank", "world", "stripe_rows")]
 
 
+class MultiConfig(C.Structure):  # ptb_multi_config
+    _fields_ = [("n_devices", C.c_int32), ("devices", C.c_int32 * 16), ("tile_groups", C.c_int32), ("stripe_rows", C.c_int32),
+                ("trace_depth", C.c_int32), ("use_graph", C.c_int32), ("megakernel", C.c_int32), ("env_nee", C.c_int32), ("reserved", C.c_int32 * 6)]
+
+
+class MultiInfo(C.Structure):  # ptb_multi_info
+    _fields_ = [(n, C.c_int32) for n in ("n_devices", "tile_groups", "sample_groups", "width", "height", "samples", "peer_stores", "reserved")]
+
+
+GATHER_HANDLE_BYTES = 64
+
+
 class Stats(C.Structure):
     _fields_ = [("extension_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("frames", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("lbvh_build_ms", C.c_float), ("lbvh_max_depth", C.c_int32),
@@ -77,6 +89,8 @@ SIGNATURES = {
     "ptb_scene_load": (C.c_int, [C.c_char_p, C.POINTER(P)]),
     "ptb_scene_from_arrays": (C.c_int, [P, P, P, P, C.c_int32, P, P, C.c_int32, P, C.c_int32, C.POINTER(Camera), C.c_int32, C.POINTER(P)]),
     "ptb_scene_set_environment": (C.c_int, [P, P, C.c_int32, C.c_int32]),
+    "ptb_scene_add_texture": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "ptb_scene_set_environment_table": (C.c_int, [P, C.c_int32, C.c_int32, P, P, C.c_int32, C.c_int32]),
     "ptb_scene_set_camera": (C.c_int, [P, C.POINTER(C.c_int32 * 2), C.c_float, C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.c_int32]),
     "ptb_scene_save_cache": (C.c_int, [P, C.c_char_p]),
     "ptb_scene_load_cache": (C.c_int, [C.c_char_p, C.POINTER(P)]),
@@ -112,6 +126,21 @@ SIGNATURES = {
     "ptb_get_stats": (C.c_int, [P, C.POINTER(Stats)]),
     "ptb_stats_reset": (C.c_int, [P]),
     "ptb_time_raycast": (C.c_int, [P, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
+    "ptb_time_kernel": (C.c_int, [P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
+    "ptb_multi_config_default": (None, [C.POINTER(MultiConfig)]),
+    "ptb_multi_init": (C.c_int, [P, C.POINTER(MultiConfig), C.POINTER(P)]),
+    "ptb_multi_free": (C.c_int, [P]),
+    "ptb_multi_render": (C.c_int, [P, C.c_int32, C.c_int32]),
+    "ptb_multi_resolve": (C.c_int, [P, P, C.c_int32, C.c_int32]),
+    "ptb_multi_sync": (C.c_int, [P]),
+    "ptb_multi_get_renderer": (C.c_int, [P, C.c_int32, C.POINTER(P)]),
+    "ptb_multi_get_info": (C.c_int, [P, C.POINTER(MultiInfo)]),
+    "ptb_gather_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(P)]),
+    "ptb_gather_export": (C.c_int, [P, P, C.c_size_t]),
+    "ptb_gather_open": (C.c_int, [C.c_int32, P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(P)]),
+    "ptb_gather_free": (C.c_int, [P]),
+    "ptb_resolve_into": (C.c_int, [P, P, C.c_int32]),
+    "ptb_gather_combine": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32, P]),
 }
 
 if not os.path.exists(LIB_PATH):

@@ -58,6 +58,7 @@ struct ptb_renderer {
     // scratch for batched tracing / timing
     void* scratch = nullptr;
     size_t scratch_bytes = 0;
+    void* flush_buf = nullptr;               // ptb_time_kernel(cold): written between launches to flush L2
     int* cursors = nullptr;                  // kMaxTimed work cursors + 1 for batches
     std::vector<int32_t> owned_pixels_cache;
 
@@ -69,6 +70,12 @@ struct ptb_renderer {
 };
 
 static constexpr int kMaxTimed = 4096;
+
+#include "renderer_internal.hpp"
+const ptb::FrameDev& ptb_internal_frame(const ptb_renderer* r) { return r->frame; }
+int ptb_internal_device(const ptb_renderer* r) { return r->device; }
+cudaStream_t ptb_internal_stream(const ptb_renderer* r) { return r->stream; }
+void ptb_internal_count_launches(ptb_renderer* r, int n) { r->kernel_launches += n; }
 
 template <typename T>
 static int dev_alloc(ptb_renderer* r, T*& p, size_t count) {
@@ -241,12 +248,15 @@ void ptb_config_default(ptb_config* cfg) {
 int ptb_free(ptb_renderer* r) {
     if (!r) return PTB_OK;
     cudaSetDevice(r->device);
-    if (r->stream) cudaStreamSynchronize(r->stream);
+    // a caller-owned stream (ptb_set_stream) may already be destroyed: only the device-wide wait is safe then
+    if (r->stream && r->own_stream) cudaStreamSynchronize(r->stream);
+    else cudaDeviceSynchronize();
     if (r->graph_exec) cudaGraphExecDestroy(r->graph_exec);
     for (cudaTextureObject_t t : r->textures) cudaDestroyTextureObject(t);
     for (cudaArray_t a : r->arrays) cudaFreeArray(a);
     for (void* p : r->allocs) cudaFree(p);
     if (r->scratch) cudaFree(r->scratch);
+    if (r->flush_buf) cudaFree(r->flush_buf);
     lbvh_free(r->lbvh);
     if (r->own_stream && r->stream) cudaStreamDestroy(r->stream);
     if (r->side) cudaStreamDestroy(r->side);
@@ -981,30 +991,64 @@ int ptb_stats_reset(ptb_renderer* r) {
     return PTB_OK;
 }
 
-int ptb_time_raycast(ptb_renderer* r, int32_t count, float* avg_ms, int32_t* rays) {
-    if (!r || !avg_ms) return fail(PTB_ERR_INVALID, "ptb_time_raycast: null argument");
-    if (count < 1 || count > kMaxTimed) return fail(PTB_ERR_INVALID, "ptb_time_raycast: count must be in [1, 4096]");
-    if (r->stage_bounce >= r->frame.trace_depth) return fail(PTB_ERR_STATE, "ptb_time_raycast: no live extension queue");
+int ptb_time_kernel(ptb_renderer* r, int32_t which, int32_t count, int32_t cold, float* avg_ms, int32_t* rays) {
+    if (!r || !avg_ms) return fail(PTB_ERR_INVALID, "ptb_time_kernel: null argument");
+    if (which != PTB_TIME_EXTENSION && which != PTB_TIME_SHADOW) return fail(PTB_ERR_INVALID, "ptb_time_kernel: unknown kernel");
+    if (count < 1 || count > kMaxTimed) return fail(PTB_ERR_INVALID, "ptb_time_kernel: count must be in [1, 4096]");
+    if (r->cfg.megakernel) return fail(PTB_ERR_STATE, "ptb_time_kernel: the megakernel path has no RayCast stage");
+    if (r->stage_bounce >= r->frame.trace_depth) return fail(PTB_ERR_STATE, "ptb_time_kernel: no live queue");
     CU(cudaSetDevice(r->device));
-    cudaEvent_t e0, e1;
-    CU(cudaEventCreate(&e0));
-    CU(cudaEventCreate(&e1));
-    CU(cudaMemsetAsync(r->cursors, 0, sizeof(int) * count, r->stream));
-    CU(cudaEventRecord(e0, r->stream));
-    for (int i = 0; i < count; i++) r->kernel_launches += launch_trace_extension_only(r->frame, r->stage_bounce, r->cursors + i, r->launch, r->stream);
-    CU(cudaEventRecord(e1, r->stream));
+    const FrameDev& f = r->frame;
+    const int b = r->stage_bounce;
+    int n = 0;
     CU(cudaStreamSynchronize(r->stream));
-    float ms = 0.0f;
-    CU(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    *avg_ms = ms / (float)count;
-    if (rays) {
-        int n = 0;
-        CU(cudaMemcpy(&n, r->frame.ctr + r->stage_bounce * CTR_STRIDE + CTR_EXT, sizeof(int), cudaMemcpyDeviceToHost));
-        *rays = n;
+    CU(cudaMemcpy(&n, f.ctr + b * CTR_STRIDE + (which == PTB_TIME_SHADOW ? CTR_SHADOW : CTR_EXT), sizeof(int), cudaMemcpyDeviceToHost));
+    if (rays) *rays = n;
+    *avg_ms = 0.0f;
+    if (which == PTB_TIME_SHADOW && (b == 0 || n == 0)) return PTB_OK;      // no shadow rays exist before the first Shade
+    const size_t kFlushBytes = (size_t)256 << 20;                             // > the 126 MB L2
+    if (cold && !r->flush_buf) CU(cudaMalloc(&r->flush_buf, kFlushBytes));
+    // the shadow kernel adds into the direct accumulator: keep a copy and put it back afterwards
+    const size_t direct_bytes = (f.env.nee ? 2 : 1) * 3 * (size_t)f.num_paths * sizeof(float);
+    if (which == PTB_TIME_SHADOW) {
+        int rc = ensure_scratch(r, direct_bytes);
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(r->scratch, f.direct, direct_bytes, cudaMemcpyDeviceToDevice, r->stream));
     }
+    std::vector<cudaEvent_t> ev(2 * (size_t)count);
+    for (auto& e : ev) CU(cudaEventCreate(&e));
+    CU(cudaMemsetAsync(r->cursors, 0, sizeof(int) * count, r->stream));
+    if (!cold) CU(cudaEventRecord(ev[0], r->stream));
+    for (int i = 0; i < count; i++) {
+        if (which == PTB_TIME_SHADOW) CU(cudaMemsetAsync(f.ctr + b * CTR_STRIDE + CTR_WORK_SHADOW, 0, sizeof(int), r->stream));
+        if (cold) {
+            CU(cudaMemsetAsync(r->flush_buf, i & 0xff, kFlushBytes, r->stream));
+            CU(cudaEventRecord(ev[2 * i], r->stream));
+        }
+        if (which == PTB_TIME_SHADOW) r->kernel_launches += launch_trace_shadow(f, b, r->launch, r->stream);
+        else r->kernel_launches += launch_trace_extension_only(f, b, r->cursors + i, r->launch, r->stream);
+        if (cold) CU(cudaEventRecord(ev[2 * i + 1], r->stream));
+    }
+    if (!cold) CU(cudaEventRecord(ev[1], r->stream));
+    if (which == PTB_TIME_SHADOW) {
+        CU(cudaMemcpyAsync(f.direct, r->scratch, direct_bytes, cudaMemcpyDeviceToDevice, r->stream));
+        CU(cudaMemsetAsync(f.ctr + b * CTR_STRIDE + CTR_WORK_SHADOW, 0, sizeof(int), r->stream));
+    }
+    CU(cudaStreamSynchronize(r->stream));
+    float total = 0.0f;
+    if (cold) {
+        for (int i = 0; i < count; i++) { float ms = 0.0f; CU(cudaEventElapsedTime(&ms, ev[2 * i], ev[2 * i + 1])); total += ms; }
+    } else {
+        CU(cudaEventElapsedTime(&total, ev[0], ev[1]));
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    *avg_ms = total / (float)count;
+    CU(cudaGetLastError());
     return PTB_OK;
+}
+
+int ptb_time_raycast(ptb_renderer* r, int32_t count, float* avg_ms, int32_t* rays) {
+    return ptb_time_kernel(r, PTB_TIME_EXTENSION, count, 0, avg_ms, rays);
 }
 
 }  // extern "C"

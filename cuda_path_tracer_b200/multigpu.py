@@ -105,3 +105,79 @@ class SampleReduce:
             if self.rank != self.dst:
                 return None
         return self.sum.div_(float(total_samples))
+
+
+class PeerUnavailable(RuntimeError):
+    """The ranks cannot map rank 0's buffer (no CUDA IPC / peer access between the GPUs): use FrameGather / SampleReduce."""
+
+
+def hybrid_layout(rank, world, tile_groups):
+    """(tile rank, sample group, sample groups) of `rank` when the world is cut into `tile_groups` stripe sets x world / tile_groups
+    sample groups: ranks 0 .. G-1 are the tiles of sample group 0, and so on."""
+    if tile_groups < 1 or world % tile_groups:
+        raise ValueError("tile_groups must divide the world size")
+    return rank % tile_groups, rank // tile_groups, world // tile_groups
+
+
+class PeerFrame:
+    """One process per GPU, NO collective on the data path: rank 0 owns the full-frame buffer (ptb_gather), exports it as a
+    CUDA IPC handle, and every rank's resolve kernel stores the pixels it owns straight into it over NVLink
+    (ptb_resolve_into).  The ranks then only need a barrier; a 4-byte all-reduce on the renderers' stream provides it in
+    stream order.  `tile_groups` G cuts the frame into G interleaved stripe sets, the other world / G factor splits the
+    sample indices (group s renders iterations s+1, s+1+S, ...); rank r is tile (r % G) of sample group (r // G).
+    Two buffers alternate by step, so a rank that runs ahead writes step k + 1 while rank 0 may still fold step k; a buffer
+    is written again only after the barrier of the step in between, which rank 0 joins after that fold (stream order).
+    The NCCL gather / reduce classes above stay as the route for boxes without peer access (PeerUnavailable)."""
+
+    def __init__(self, width, height, dist, device_index, tile_groups=0, stripe_rows=8):
+        import torch
+        from .capi import PtbError
+        from .wavefront import Gather
+        self.dist, self.torch = dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.tile_groups = tile_groups or self.world
+        self.tile_rank, self.sample_group, self.sample_groups = hybrid_layout(self.rank, self.world, self.tile_groups)
+        self.stripe_rows, self.width, self.height = stripe_rows, width, height
+        self.token = torch.zeros(1, dtype=torch.float32, device=torch.device("cuda", device_index))
+        self.gathers, ok = [], 1.0
+        handles = [None]
+        try:
+            if self.rank == 0:
+                self.gathers = [Gather(device_index, width, height, self.sample_groups) for _ in range(2)]
+                handles[0] = [g.export() for g in self.gathers]
+        except PtbError:
+            ok = 0.0
+        dist.broadcast_object_list(handles, src=0)
+        if self.rank != 0:
+            try:
+                self.gathers = [Gather.open(device_index, h, width, height, self.sample_groups) for h in (handles[0] or [])]
+                ok = 1.0 if len(self.gathers) == 2 else 0.0
+            except PtbError:
+                ok = 0.0
+        flag = torch.tensor([ok], dtype=torch.float32, device=self.token.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if float(flag[0]) < 1.0:
+            self.free()
+            raise PeerUnavailable("rank 0's frame buffer cannot be mapped by every rank")
+
+    def renderer_kwargs(self):
+        """Keyword arguments of wavefront.Renderer for this rank's share of the frame."""
+        return dict(rank=self.tile_rank, world=self.tile_groups, stripe_rows=self.stripe_rows)
+
+    def iteration(self, step):
+        """1-based iteration this rank renders at 0-based step `step`."""
+        return step * self.sample_groups + self.sample_group + 1
+
+    def submit(self, renderer, step):
+        """Store this rank's pixels into rank 0's buffer of `step` and join the barrier (both on the current CUDA stream)."""
+        self.gathers[step & 1].resolve_from(renderer, self.sample_group)
+        self.dist.all_reduce(self.token)
+
+    def combine_device(self, device_ptr, steps, fmt, stream, step):
+        """Rank 0, after submit(step): fold the sample groups and write the frame (steps * sample_groups samples per pixel)."""
+        self.gathers[step & 1].combine_device(device_ptr, steps * self.sample_groups, fmt, stream)
+
+    def free(self):
+        for g in self.gathers:
+            g.free()
+        self.gathers = []

@@ -308,6 +308,77 @@ def heightfield_arrays(num_triangles, seed=7, extent=40.0):
     return pos, nor, idx, mat
 
 
+def _fixed_floats(a, int_digits=4, frac_digits=6):
+    """(n, k) floats -> (n, k * width) ASCII bytes ' -dddd.dddddd' per value (fixed width, leading zeros), vectorised."""
+    a = np.asarray(a, np.float64)
+    q = np.rint(np.abs(a) * 10 ** frac_digits).astype(np.int64)
+    width = 2 + int_digits + 1 + frac_digits
+    out = np.empty(a.shape + (width,), np.uint8)
+    out[..., 0] = ord(" ")
+    out[..., 1] = np.where((a < 0) & (q > 0), ord("-"), ord("+"))
+    col = width - 1
+    for k in range(frac_digits):
+        out[..., col] = ord("0") + q % 10; q //= 10; col -= 1
+    out[..., col] = ord("."); col -= 1
+    for k in range(int_digits):
+        out[..., col] = ord("0") + q % 10; q //= 10; col -= 1
+    return out.reshape(a.shape[0], -1)
+
+
+def write_obj_fast(path, p, n, tris):
+    """The same OBJ dialect as write_obj (v / vn per vertex, `f a//a b//b c//c`) in fixed-width fields built with numpy, for
+    meshes of millions of triangles (10 M triangles: ~0.9 GB of text in a few seconds instead of minutes)."""
+    nv, nt = len(p), len(tris)
+    with open(path, "wb") as f:
+        for tag, arr in ((b"v", p), (b"vn", n)):
+            body = _fixed_floats(arr, 4 if tag == b"v" else 1)
+            line = np.empty((nv, len(tag) + body.shape[1] + 1), np.uint8)
+            line[:, :len(tag)] = np.frombuffer(tag, np.uint8)
+            line[:, len(tag):-1] = body
+            line[:, -1] = ord("\n")
+            f.write(line.tobytes())
+        t1 = np.asarray(tris, np.int64) + 1
+        digits = 8
+        idx = np.empty((nt, 3, digits), np.uint8)
+        q = t1.copy()
+        for k in range(digits - 1, -1, -1):
+            idx[..., k] = ord("0") + q % 10; q //= 10
+        # "f A//A B//B C//C\n"
+        line = np.empty((nt, 1 + 3 * (1 + digits + 2 + digits) + 1), np.uint8)
+        line[:, 0] = ord("f")
+        c = 1
+        for v in range(3):
+            line[:, c] = ord(" "); c += 1
+            line[:, c:c + digits] = idx[:, v]; c += digits
+            line[:, c] = ord("/"); line[:, c + 1] = ord("/"); c += 2
+            line[:, c:c + digits] = idx[:, v]; c += digits
+        line[:, c] = ord("\n")
+        f.write(line.tobytes())
+
+
+def stress_scene(out_dir, num_triangles=10_000_000, res=(1920, 1080), depth=8):
+    """BASELINE config[3] in scene-file form (what the reference's own loader can read): the height field + micro-triangles of
+    heightfield_arrays() written as one OBJ per material, the five stress materials and the stress camera."""
+    os.makedirs(out_dir, exist_ok=True)
+    pos, nor, idx, mat = heightfield_arrays(num_triangles)
+    names = ["a_ground", "b_gold", "c_glass", "d_blue", "e_lamp"]
+    spec = {"a_ground": _mat([0.55, 0.5, 0.42]), "b_gold": _mat([0.9, 0.6, 0.2], "MicrofacetPBR", metallic=1.0, roughness=0.3),
+            "c_glass": _mat([0.95, 0.97, 1.0], "SPECULAR_REFRACTION", ior=1.5), "d_blue": _mat([0.2, 0.5, 0.8]),
+            "e_lamp": _mat([1.0, 0.95, 0.85], emittance=40.0)}
+    objs = []
+    for m, name in enumerate(names):
+        t = idx[mat == m]
+        used, inv = np.unique(t.reshape(-1), return_inverse=True)
+        path = os.path.join(out_dir, name + ".obj")
+        write_obj_fast(path, pos[used], nor[used], inv.reshape(-1, 3))
+        objs.append(_obj_entry(path, name))
+    c = stress_camera(res)
+    cam = {"RES": list(res), "FOVY": c["fovy"], "ITERATIONS": 4, "DEPTH": depth, "FILE": "stress", "EYE": c["eye"], "LOOKAT": c["look_at"], "UP": c["up"]}
+    path = os.path.join(out_dir, "scene.json")
+    write_scene(path, cam, spec, objs)
+    return path, len(idx)
+
+
 def stress_materials():
     from .capi import MATERIAL_DTYPE
     m = np.zeros(5, MATERIAL_DTYPE)
@@ -322,6 +393,85 @@ def stress_materials():
 
 def stress_camera(res=(1920, 1080)):
     return dict(resolution=res, fovy=50.0, eye=[0.0, 14.0, 38.0], look_at=[0.0, 2.0, 0.0], up=[0.0, 1.0, 0.0])
+
+
+# ------------------------------------------------------------------------------------ deep LBVH: the 32-entry stack abort
+def deepchain(out_dir, res=(160, 120), depth=4, fovy=70.0):
+    """A scene whose LBVH is a CHAIN deeper than the 32 entries the reference's closest-hit walk stacks before it gives up
+    (src/kernels/ray_cast.cu:35,106), arranged so that camera rays really run into that limit.
+
+    Keys are (30-bit Morton code << 32) | triangle index (src/bvh.cu:95) and Karras' hierarchy splits at the highest
+    differing bit, so a chain needs keys that differ from one anchor key in exactly one bit each:
+      * three slivers along the axes pin the scene box to [0, 1]^3 (codes are then exact binary fractions);
+      * Q = (1/2, 1/2, 1/2) has code 111 000 ... 0; "marker" k (k = 0..26) is one triangle whose AABB centre is Q plus
+        2^-(2 + k/3) on axis k % 3: its code is Q's with bit 26 - k set -- 27 chain levels from the code bits;
+      * a cluster of triangles centred in Q's own cell takes the triangle indices 0, 1, 2, 4, ..., 256: identical codes,
+        so the index bits continue the chain for 9 more levels.
+    The camera sits at Q looking along (1, 1, 1): it is inside every "rest of the chain" box (entry distance 0) and just
+    outside most marker boxes, which lie ahead and are all crossed by rays near the diagonal -- so the walk descends
+    near-first into the chain and stacks one marker per level.  Markers 3..5 contain the eye (a tie: the
+    right child, the marker, is tested first), so some rays give up holding a hit, others holding none."""
+    os.makedirs(out_dir, exist_ok=True)
+    Q = 0.5
+    tris = {}                                   # triangle index -> (3, 3) vertices
+    kind = {}                                   # triangle index -> material name
+
+    def corner_tri(lo, hi):
+        lo, hi = np.asarray(lo, np.float64), np.asarray(hi, np.float64)
+        return np.array([[lo[0], hi[1], hi[2]], [hi[0], lo[1], hi[2]], [hi[0], hi[1], lo[2]]])   # the far diagonal of the box
+
+    def axis_box(axis, s, eye_inside):
+        lo = np.full(3, Q - 0.9 * s); hi = np.full(3, Q + 0.9 * s)
+        lo[axis] = Q + (-0.1 if eye_inside else 0.1) * s
+        hi[axis] = 2.0 * (Q + s) - lo[axis]      # AABB centre on this axis = Q + s exactly
+        return lo, hi
+
+    cluster_ids = [0, 1, 2, 4, 8, 16, 32, 64, 128, 256]
+    cell = 1.0 / 1024.0
+    for j, tid in enumerate(cluster_ids):        # centres inside Q's cell: same 30-bit code, order decided by the index
+        s = cell * 0.45 * (j + 1) / len(cluster_ids)
+        lo, hi = axis_box(j % 3, s, False)
+        tris[tid] = corner_tri(lo, hi); kind[tid] = "white"
+    free = [i for i in range(320) if i not in tris]
+    it = iter(free)
+    for k in range(27):
+        s = 2.0 ** -(2 + k // 3)
+        lo, hi = axis_box(k % 3, s, 3 <= k < 6)
+        tid = next(it)
+        tris[tid] = corner_tri(lo, hi); kind[tid] = "lamp" if k == 10 else ("red" if k % 2 else "white")   # a mid-chain marker lights the larger ones behind it
+    eps = 1.0 / 4096.0
+    for a in range(3):                           # slivers along the axes: scene box = [0, 1]^3, centres outside Q's octant
+        v = np.zeros((3, 3)); v[1, a] = 1.0; v[2, a] = 0.5; v[2, (a + 1) % 3] = eps; v[1, (a + 2) % 3] = eps
+        tid = next(it)
+        tris[tid] = v; kind[tid] = "white"
+    rng = np.random.RandomState(11)
+    for tid in it:                               # filler in the x < 1/2 half: small triangles the camera never sees
+        c = rng.uniform([0.05, 0.05, 0.05], [0.4, 0.9, 0.9])
+        tris[tid] = c + rng.uniform(-0.02, 0.02, (3, 3)); kind[tid] = "green"
+    n = len(tris)
+    P = np.concatenate([tris[i] for i in range(n)]).astype(np.float64)
+    Nn = np.repeat(np.array([np.cross(tris[i][1] - tris[i][0], tris[i][2] - tris[i][0]) for i in range(n)]), 3, axis=0)
+    Nn /= np.maximum(np.linalg.norm(Nn, axis=1, keepdims=True), 1e-30)
+    T = np.arange(3 * n).reshape(-1, 3)
+    # %.6f would move the corners: write the vertices with enough digits to round-trip float32
+    lines = ["v %.9g %.9g %.9g" % tuple(np.float32(r)) for r in P] + ["vn %.6f %.6f %.6f" % tuple(r) for r in Nn]
+    cur = None
+    for i, (a, b, c) in enumerate(T + 1):
+        if kind[i] != cur:
+            cur = kind[i]
+            lines.append(f"usemtl {cur}")
+        lines.append(f"f {a}//{a} {b}//{b} {c}//{c}")
+    mtl = {"white": [0.73, 0.73, 0.73], "red": [0.65, 0.05, 0.05], "green": [0.12, 0.45, 0.15], "lamp": [1.0, 0.9, 0.7]}
+    with open(os.path.join(out_dir, "chain.mtl"), "w") as f:
+        for name, kd in mtl.items():
+            f.write(f"newmtl {name}\nKd {kd[0]} {kd[1]} {kd[2]}\n" + ("Ke 14 12 9\n" if name == "lamp" else "") + "\n")
+    with open(os.path.join(out_dir, "chain.obj"), "w") as f:
+        f.write("mtllib chain.mtl\n" + "\n".join(lines) + "\n")
+    cam = {"RES": list(res), "FOVY": fovy, "ITERATIONS": 4, "DEPTH": depth, "FILE": "deepchain",
+           "EYE": [Q, Q, Q], "LOOKAT": [1.0, 1.0, 1.0], "UP": [0.0, 1.0, 0.0]}
+    path = os.path.join(out_dir, "scene.json")
+    write_scene(path, cam, {"unused": _mat([0.5, 0.5, 0.5])}, [_obj_entry(os.path.join(out_dir, "chain.obj"))])
+    return path
 
 
 # ------------------------------------------------------------------------------------ config 3

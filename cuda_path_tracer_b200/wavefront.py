@@ -248,6 +248,12 @@ class Renderer:
         check(lib.ptb_time_raycast(self._h, count, C.byref(ms), C.byref(rays)))
         return ms.value, rays.value
 
+    def time_kernel(self, which, count, cold=False):
+        """(avg ms, rays) of `count` launches of the extension ('ext') or shadow ('shadow') RayCast kernel of the current bounce."""
+        ms, rays = C.c_float(), C.c_int32()
+        check(lib.ptb_time_kernel(self._h, {"ext": 0, "shadow": 1}[which], count, int(cold), C.byref(ms), C.byref(rays)))
+        return ms.value, rays.value
+
     def stats(self):
         s = capi.Stats()
         check(lib.ptb_get_stats(self._h, C.byref(s)))
@@ -259,6 +265,114 @@ class Renderer:
     def free(self):
         if self._h:
             check(lib.ptb_free(self._h))
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class MultiRenderer:
+    """ptb_multi: one frame over several GPUs of ONE process (include/ptb200.h, multi-GPU).  `devices[0]` is the root; the
+    resolve kernel of every GPU stores its pixels into the root's frame buffer over NVLink.  tile_groups G cuts the frame into
+    G interleaved stripe sets, the remaining len(devices) / G factor splits the sample indices."""
+
+    def __init__(self, scene, devices, tile_groups=0, stripe_rows=8, trace_depth=0, use_graph=True, megakernel=False, env_nee=False):
+        cfg = capi.MultiConfig()
+        lib.ptb_multi_config_default(C.byref(cfg))
+        cfg.n_devices = len(devices)
+        for k, d in enumerate(devices):
+            cfg.devices[k] = d
+        cfg.tile_groups, cfg.stripe_rows, cfg.trace_depth = tile_groups, stripe_rows, trace_depth
+        cfg.use_graph, cfg.megakernel, cfg.env_nee = int(use_graph), int(megakernel), int(env_nee)
+        self._h = C.c_void_p()
+        check(lib.ptb_multi_init(scene._h, C.byref(cfg), C.byref(self._h)))
+        i = self.info
+        self.width, self.height, self.tile_groups, self.sample_groups = i.width, i.height, i.tile_groups, i.sample_groups
+
+    @property
+    def info(self):
+        i = capi.MultiInfo()
+        check(lib.ptb_multi_get_info(self._h, C.byref(i)))
+        return i
+
+    def render(self, first_step, count=1):
+        check(lib.ptb_multi_render(self._h, first_step, count))
+
+    def resolve(self, fmt=capi.IMG_MEAN_RGB32F, out=None):
+        n = self.width * self.height
+        if out is None:
+            out = np.empty((n, 4), np.uint8) if fmt == capi.IMG_RGBA8 else np.empty((n, 3), np.float32)
+        check(lib.ptb_multi_resolve(self._h, ptr(out), fmt, 0))
+        return out
+
+    def resolve_device(self, device_ptr, fmt=capi.IMG_MEAN_RGB32F):
+        check(lib.ptb_multi_resolve(self._h, C.c_void_p(device_ptr), fmt, 1))
+
+    def sync(self):
+        check(lib.ptb_multi_sync(self._h))
+
+    def stats(self, index):
+        h = C.c_void_p()
+        check(lib.ptb_multi_get_renderer(self._h, index, C.byref(h)))
+        s = capi.Stats()
+        check(lib.ptb_get_stats(h, C.byref(s)))
+        return s
+
+    def free(self):
+        if self._h:
+            check(lib.ptb_multi_free(self._h))
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Gather:
+    """ptb_gather: the root's full-frame buffer other ranks' resolve kernels store into (one process per GPU: export() on the
+    root, Gather.open(handle) elsewhere)."""
+
+    def __init__(self, device, width, height, slices=1, _handle=None, _remote=False):
+        self.device, self.width, self.height, self.slices, self.remote = device, width, height, slices, _remote
+        self._h = C.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+        else:
+            check(lib.ptb_gather_create(device, width, height, slices, C.byref(self._h)))
+
+    def export(self):
+        buf = C.create_string_buffer(capi.GATHER_HANDLE_BYTES)
+        check(lib.ptb_gather_export(self._h, buf, capi.GATHER_HANDLE_BYTES))
+        return buf.raw
+
+    @classmethod
+    def open(cls, device, handle, width, height, slices=1):
+        h = C.c_void_p()
+        buf = C.create_string_buffer(bytes(handle), capi.GATHER_HANDLE_BYTES)
+        check(lib.ptb_gather_open(device, buf, width, height, slices, C.byref(h)))
+        return cls(device, width, height, slices, _handle=h, _remote=True)
+
+    def resolve_from(self, renderer, slice_index=0):
+        check(lib.ptb_resolve_into(renderer._h, self._h, slice_index))
+
+    def combine(self, samples, fmt=capi.IMG_MEAN_RGB32F, out=None, stream=0):
+        n = self.width * self.height
+        if out is None:
+            out = np.empty((n, 4), np.uint8) if fmt == capi.IMG_RGBA8 else np.empty((n, 3), np.float32)
+        check(lib.ptb_gather_combine(self._h, ptr(out), fmt, samples, 0, C.c_void_p(stream)))
+        return out
+
+    def combine_device(self, device_ptr, samples, fmt=capi.IMG_MEAN_RGB32F, stream=0):
+        check(lib.ptb_gather_combine(self._h, C.c_void_p(device_ptr), fmt, samples, 1, C.c_void_p(stream)))
+
+    def free(self):
+        if self._h:
+            check(lib.ptb_gather_free(self._h))
             self._h = C.c_void_p()
 
     def __del__(self):

@@ -246,6 +246,63 @@ int ptb_get_tile_info(const ptb_renderer* r, ptb_tile_info* out);
 /* Global pixel index of every owned pixel, in the order ptb_resolve / ptb_get_accumulators use. */
 int ptb_get_owned_pixels(const ptb_renderer* r, int32_t* dst, int32_t capacity);
 
+/* ---------------------------------------------------------------- multi-GPU */
+/* New (the reference renders on device 0 of one process, src/main.cpp:168).  Every GPU keeps a scene + LBVH replica and
+ * renders a share of the frame; the resolve kernel of each GPU (the counterpart of SendImageToPBOKernel,
+ * src/pathtrace_wavefront.cu:47-116) writes the sums of the pixels it owns directly into ONE full-frame buffer on the root
+ * GPU through NVLink peer stores, so the gather is the tail of that kernel and no collective library sits on the data
+ * path.  Two partitions compose: `tile_groups` G interleaved stripe sets of the frame (ptb_config.rank / world, bit-identical
+ * to one GPU) x `n_devices / G` sample groups (group s renders iterations s+1, s+1+S, ...; their sums are folded on the
+ * root in group order, so the result is deterministic and differs from one GPU only in float summation order). */
+#define PTB_MAX_DEVICES 16
+typedef struct ptb_multi ptb_multi;
+typedef struct ptb_multi_config {
+    int32_t n_devices;                    /* 1 .. PTB_MAX_DEVICES */
+    int32_t devices[PTB_MAX_DEVICES];     /* CUDA ordinals; devices[0] is the root: it owns the gathered frame.  An ordinal may
+                                             appear more than once (several renderers then share that GPU) */
+    int32_t tile_groups;                  /* G; 0 = n_devices (pure tile partition); must divide n_devices */
+    int32_t stripe_rows;                  /* rows per stripe of the tile partition (default 8) */
+    int32_t trace_depth, use_graph, megakernel, env_nee;   /* as in ptb_config */
+    int32_t reserved[6];
+} ptb_multi_config;
+typedef struct ptb_multi_info {
+    int32_t n_devices, tile_groups, sample_groups;
+    int32_t width, height;
+    int32_t samples;                      /* samples per pixel accumulated so far */
+    int32_t peer_stores;                  /* devices whose resolve kernel stores into the root's memory (the others copy) */
+    int32_t reserved;
+} ptb_multi_info;
+void ptb_multi_config_default(ptb_multi_config* cfg);
+/* PathtraceInit on every listed device (scene upload + LBVH build per GPU) + the root's frame buffer + peer access. */
+int ptb_multi_init(const ptb_scene* scene, const ptb_multi_config* cfg, ptb_multi** out);
+int ptb_multi_free(ptb_multi* m);
+/* Steps first .. first+count-1 (1-based; step 1 restarts the accumulation).  One step adds `sample_groups` samples per pixel:
+ * device k (tile group k % G, sample group k / G) renders iteration (step-1)*S + k/G + 1 of its stripes.  Asynchronous. */
+int ptb_multi_render(ptb_multi* m, int32_t first_step, int32_t count);
+/* Gather + fold + format into `dst` (full frame: width*height float3, or uchar4 for PTB_IMG_RGBA8), on the root device
+ * (dst_on_device != 0, asynchronous on the root's stream; ptb_multi_sync waits) or on the host (synchronous). */
+int ptb_multi_resolve(ptb_multi* m, void* dst, int32_t format, int32_t dst_on_device);
+int ptb_multi_sync(ptb_multi* m);
+/* The per-device renderer (statistics, parity views); owned by the ptb_multi. */
+int ptb_multi_get_renderer(ptb_multi* m, int32_t index, ptb_renderer** out);
+int ptb_multi_get_info(const ptb_multi* m, ptb_multi_info* out);
+
+/* The same gather for ONE PROCESS PER GPU (torchrun): the root rank creates the full-frame buffer and exports it as a CUDA
+ * IPC handle; every other rank opens it and its resolve kernel stores into the root's memory over NVLink.  The ranks
+ * only need a barrier between ptb_resolve_into and the root's ptb_gather_combine (cuda_path_tracer_b200/multigpu.py uses
+ * a 4-byte NCCL all-reduce on the renderers' stream).  slices = sample groups (1 for a pure tile partition). */
+#define PTB_GATHER_HANDLE_BYTES 64
+typedef struct ptb_gather ptb_gather;
+int ptb_gather_create(int32_t device, int32_t width, int32_t height, int32_t slices, ptb_gather** out);
+int ptb_gather_export(ptb_gather* g, void* handle, size_t bytes);
+int ptb_gather_open(int32_t device, const void* handle, int32_t width, int32_t height, int32_t slices, ptb_gather** out);
+int ptb_gather_free(ptb_gather* g);
+/* direct + indirect of every pixel the renderer owns -> slice `slice` of the buffer, at the pixels' global positions. */
+int ptb_resolve_into(ptb_renderer* r, ptb_gather* g, int32_t slice);
+/* Root only: fold the slices in order and write `format` (PTB_IMG_SUM_RGB32F / _MEAN_RGB32F / _RGBA8; `samples` = samples
+ * per pixel the sums hold) on cuda_stream (cudaStream_t as void*); host destinations are synchronous. */
+int ptb_gather_combine(ptb_gather* g, void* dst, int32_t format, int32_t samples, int32_t dst_on_device, void* cuda_stream);
+
 /* ------------------------------------------------------- LBVH (parity view) */
 /* The LBVH in the reference's own layout (`LBVHData`, src/scene_structs.h:151-169): node index
  * space [0,N-2] internal, N-1 gap, [N,2N-1] leaves; leaf children stored bit-inverted. */
@@ -340,6 +397,12 @@ int ptb_stats_reset(ptb_renderer* r);
  * Results are discarded-safe: the kernel is idempotent on the same queue.  Used by bench.py
  * for the roofline figure. */
 int ptb_time_raycast(ptb_renderer* r, int32_t count, float* avg_ms, int32_t* rays);
+/* The same for either RayCast kernel of the current bounce: PTB_TIME_EXTENSION (TraceExtensionRayKernel's counterpart alone,
+ * without the fused Logic) or PTB_TIME_SHADOW (TraceShadowRayKernel's; the direct accumulator it adds into is saved and
+ * restored, so the frame is unchanged; 0 rays / 0 ms before the first Shade).  cold != 0: a 256 MB write flushes the L2
+ * before every launch and each launch is timed by its own event pair; cold == 0: back-to-back launches, tree warm in L2. */
+enum { PTB_TIME_EXTENSION = 0, PTB_TIME_SHADOW = 1 };
+int ptb_time_kernel(ptb_renderer* r, int32_t which, int32_t count, int32_t cold, float* avg_ms, int32_t* rays);
 
 #ifdef __cplusplus
 }

@@ -30,6 +30,59 @@ namespace pathtrace_megakernel {   // ref_mega_access.cu
 }
 
 static std::string g_out;
+static void dump_dev(const std::string& name, const void* dev, size_t bytes);
+
+// sampleEnvironmentMap (src/interactions.cu:447-488) is defined in the reference but declared in no header and called by
+// nothing; the build is -rdc, so a declaration here links against the reference's own definition.
+__device__ float3 sampleEnvironmentMap(const EnvMapAliasTable env, cudaTextureObject_t* d_texture_objects, float2 rnd, float& pdf);
+__global__ void SampleEnvKernel(EnvMapAliasTable env, cudaTextureObject_t* tex, const float2* rnd, int n, float3* dir, float* pdf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float p = 0.0f;
+    float3 d = sampleEnvironmentMap(env, tex, rnd[i], p);
+    dir[i] = d;
+    pdf[i] = p;
+}
+// --sample-env RND.bin: the reference's own sampler over the caller's random pairs -> env_dir.bin / env_pdf.bin
+static int sample_env(Scene* scene, const std::string& rnd_file) {
+    if (scene->env_map.width <= 0) { fprintf(stderr, "refdump: scene has no environment map\n"); return 5; }
+    FILE* f = fopen(rnd_file.c_str(), "rb");
+    if (!f) { fprintf(stderr, "refdump: cannot read %s\n", rnd_file.c_str()); return 5; }
+    fseek(f, 0, SEEK_END); long bytes = ftell(f); fseek(f, 0, SEEK_SET);
+    const int n = (int)(bytes / sizeof(float2));
+    std::vector<float2> rnd(n);
+    if (fread(rnd.data(), sizeof(float2), n, f) != (size_t)n) { fclose(f); return 5; }
+    fclose(f);
+    const size_t N = (size_t)scene->env_map.width * scene->env_map.height;
+    EnvMapAliasTable env;
+    env.width = scene->env_map.width; env.height = scene->env_map.height;
+    env.pdf_map_id = scene->env_map.pdf_map_id; env.env_tex_id = scene->env_map.env_tex_id;
+    float* d_probs; int* d_aliases; cudaTextureObject_t* d_tex; float2* d_rnd; float3* d_dir; float* d_pdf;
+    cudaMalloc(&d_probs, N * sizeof(float)); cudaMalloc(&d_aliases, N * sizeof(int));
+    cudaMemcpy(d_probs, scene->env_map.probs.data(), N * sizeof(float), cudaMemcpyHostToDevice);     // the upload the reference's
+    cudaMemcpy(d_aliases, scene->env_map.aliases.data(), N * sizeof(int), cudaMemcpyHostToDevice);   // initEnvAliasTable leaves out
+    env.probs = d_probs; env.aliases = d_aliases;
+    cudaMalloc(&d_tex, scene->texture_handles.size() * sizeof(cudaTextureObject_t));
+    cudaMemcpy(d_tex, scene->texture_handles.data(), scene->texture_handles.size() * sizeof(cudaTextureObject_t), cudaMemcpyHostToDevice);
+    cudaMalloc(&d_rnd, n * sizeof(float2)); cudaMalloc(&d_dir, n * sizeof(float3)); cudaMalloc(&d_pdf, n * sizeof(float));
+    cudaMemcpy(d_rnd, rnd.data(), n * sizeof(float2), cudaMemcpyHostToDevice);
+    SampleEnvKernel<<<(n + 255) / 256, 256>>>(env, d_tex, d_rnd, n, d_dir, d_pdf);
+    cudaError_t e = cudaDeviceSynchronize();
+    dump_dev("env_dir", d_dir, n * sizeof(float3));
+    dump_dev("env_pdf", d_pdf, n * sizeof(float));
+    printf("REFENV {\"samples\": %d, \"cuda\": \"%s\"}\n", n, cudaGetErrorString(e));
+    return e == cudaSuccess ? 0 : 4;
+}
+
+// position-weighted word sum of a device array (the --load-only checksum): what a 10 M-triangle run compares instead of
+// writing gigabytes of dumps
+static unsigned long long sum_dev(const void* dev, size_t bytes) {
+    std::vector<unsigned int> h(bytes / 4 ? bytes / 4 : 1);
+    if (bytes) cudaMemcpy(h.data(), dev, bytes, cudaMemcpyDeviceToHost);
+    unsigned long long s = 0;
+    for (size_t i = 0; i < bytes / 4; i++) s += ((unsigned long long)h[i] + 1ull) * ((unsigned long long)i * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull);
+    return s;
+}
 
 static void dump_raw(const std::string& name, const void* host, size_t bytes) {
     std::string p = g_out + "/" + name + ".bin";
@@ -202,7 +255,8 @@ int main(int argc, char** argv) {
     int iters = 1, bench_k = 0, bench_w = 0;
     bool stages = false, selfcheck = false, mega = false, no_dump = false, views = false, denoise = false;
     int bench_d = 0;
-    bool load_only = false;
+    bool load_only = false, sums = false;
+    std::string env_rnd;
     for (int i = 3; i < argc; i++) {
         std::string a = argv[i];
         if (a == "--iters" && i + 1 < argc) iters = atoi(argv[++i]);
@@ -212,6 +266,8 @@ int main(int argc, char** argv) {
         else if (a == "--no-dump") no_dump = true;
         else if (a == "--views") views = true;
         else if (a == "--denoise") denoise = true;
+        else if (a == "--sample-env" && i + 1 < argc) env_rnd = argv[++i];   // the reference's sampleEnvironmentMap over the pairs in this file
+        else if (a == "--sums") sums = true;                                 // print checksums of the LBVH / accumulators instead of dumping them
         else if (a == "--load-only") load_only = true;   // time the reference's scene loader (host only) and stop
         else if (a == "--denoise-bench" && i + 1 < argc) { denoise = true; bench_d = atoi(argv[++i]); }
         else if (a == "--bench" && i + 2 < argc) { bench_k = atoi(argv[++i]); bench_w = atoi(argv[++i]); }
@@ -240,6 +296,7 @@ int main(int argc, char** argv) {
     }
     const Camera& cam = scene->state.camera;
     const int P = cam.resolution.x * cam.resolution.y;
+    if (!env_rnd.empty()) return sample_env(scene, env_rnd);
 
     GuiDataContainer gui;
     gui.DenoiserOn = false;   // ctor default is true, which would switch the frame to SVGF 1-spp mode
@@ -279,6 +336,17 @@ int main(int argc, char** argv) {
     double t_init = now_s() - t_init0;
     WavefrontPathTracerState* st = pathtrace_wavefront::OracleState();
     if (!no_dump) dump_scene_and_bvh(scene, st);
+    if (sums) {
+        const size_t N = st->d_mesh_data.num_triangles, V = st->d_mesh_data.num_vertices;
+        const LBVHData& b = st->d_bvh_data;
+        printf("REFSUMS {\"num_triangles\": %zu, \"num_vertices\": %zu, \"load_s\": %.3f, \"init_s\": %.3f, "
+               "\"pos\": \"%016llx\", \"indices_matid\": \"%016llx\", \"aabb_min\": \"%016llx\", \"aabb_max\": \"%016llx\", \"centroid\": \"%016llx\", "
+               "\"primitive_indices\": \"%016llx\", \"morton_codes\": \"%016llx\", \"child_nodes\": \"%016llx\", \"parent\": \"%016llx\", \"escape_indices\": \"%016llx\"}\n",
+               N, V, t_load, t_init, sum_dev(st->d_mesh_data.pos, V * 16), sum_dev(st->d_mesh_data.indices_matid, N * 16),
+               sum_dev(b.aabb_min, 2 * N * 16), sum_dev(b.aabb_max, 2 * N * 16), sum_dev(b.centroid, 2 * N * 16), sum_dev(b.primitive_indices, 2 * N * 4),
+               sum_dev(b.morton_codes, N * 8), sum_dev(b.child_nodes, (N - 1) * 8), sum_dev(b.parent, 2 * N * 4), sum_dev(b.escape_indices, 2 * N * 4));
+        fflush(stdout);
+    }
 
     if (bench_k > 0) {
         double mr = 0;

@@ -18,9 +18,35 @@ def have_refdump():
     return os.path.exists(REFDUMP) and os.access(REFDUMP, os.X_OK)
 
 
-def run_refdump(scene_json, out_dir, iters=1, stages=True, selfcheck=False, timeout=900, views=False, denoise=False, mega=False):
+SHIMDUMP = os.path.join(ROOT, "oracle", "_ref", "shimdump")
+
+
+def word_sum(a):
+    """refdump --sums / --load-only checksum of an array: position-weighted sum of its 32-bit words (wrapping uint64)."""
+    w = np.ascontiguousarray(a).view(np.uint32).reshape(-1).astype(np.uint64)
+    n = np.arange(w.size, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        h = ((w + np.uint64(1)) * (n * np.uint64(0x9E3779B97F4A7C15) + np.uint64(0x632BE59BD9B4E019))).sum(dtype=np.uint64)
+    return "%016x" % int(h)
+
+
+def run_shimdump(scene_json, out_dir, iters, mode="file", pbo=True, timeout=600):
+    """The reference's headless loop over the SHIM (shim/pathtrace_wavefront_ptb200.cpp compiled against the reference's
+    unchanged headers, oracle/Makefile): returns (direct, indirect, pbo or None)."""
     os.makedirs(out_dir, exist_ok=True)
-    cmd = [REFDUMP, scene_json, out_dir, "--iters", str(iters)]
+    env = dict(os.environ, PTB_SHIM_SCENE=mode)
+    p = subprocess.run([SHIMDUMP, scene_json, out_dir, str(iters)] + (["--pbo"] if pbo else []), capture_output=True, text=True, timeout=timeout, env=env)
+    if p.returncode != 0 or "SHIMDUMP" not in p.stdout:
+        raise RuntimeError(f"shimdump failed ({p.returncode}):\n{p.stdout[-2000:]}\n{p.stderr[-2000:]}")
+    d = np.fromfile(os.path.join(out_dir, "direct.bin"), dtype="<f4").reshape(-1, 3)
+    i = np.fromfile(os.path.join(out_dir, "indirect.bin"), dtype="<f4").reshape(-1, 3)
+    px = np.fromfile(os.path.join(out_dir, "pbo.bin"), dtype="u1").reshape(-1, 4) if pbo else None
+    return d, i, px
+
+
+def run_refdump(scene_json, out_dir, iters=1, stages=True, selfcheck=False, timeout=900, views=False, denoise=False, mega=False, extra=()):
+    os.makedirs(out_dir, exist_ok=True)
+    cmd = [REFDUMP, scene_json, out_dir, "--iters", str(iters)] + list(extra)
     if stages:
         cmd.append("--stages")
     if selfcheck:

@@ -287,6 +287,105 @@ def test_stress_10m_lbvh_and_raycast_vs_oracle():
     r.free()
 
 
+def test_deep_tree_stack_abort_vs_reference(tmp_path):
+    """The reference's closest-hit walk gives up with the best hit so far once 32 entries are stacked
+    (src/kernels/ray_cast.cu:106).  scenegen.deepchain builds an LBVH 38 levels deep in which most camera rays run into
+    that limit (58 % of the pixels show a hit that is NOT the closest one), so the reference's own abort is what pins
+    raycast.cuh's: every stage of every bounce, both accumulators and the megakernel image, bit for bit."""
+    _need_ref()
+    scene_json = scenegen.deepchain(str(tmp_path / "chain"), res=(160, 120), depth=4)
+    s = ptb.Scene(scene_json)
+    pos, im = s.array("pos"), s.array("indices_matid")
+    d = str(tmp_path / "ref")
+    log = par.run_refdump(scene_json, d, iters=2, stages=True, selfcheck=True)
+    assert '"mismatching_floats": 0' in log
+    ref = par.RefDump(d)
+    assert all(par.compare_scene(ref, s).values())
+    r = ptb.Renderer(s)
+    assert r.stats().lbvh_max_depth > 32
+    assert all(par.compare_lbvh(ref, r).values())
+    # the limit is live: the CPU restatement, which counts stack use, reaches 32 on the camera rays of this frame
+    r.stage(capi.STAGE_RAYGEN, 1)
+    ori, dirs = r.path_field("ray_ori"), r.path_field("ray_dir_dist")
+    bvh = {k: r.lbvh(k) for k in LBVH_NAMES}
+    hit_cpu, _, _, _ = orc.trace_closest(bvh, pos, im, ori, dirs, threads=8)
+    assert orc.trace_closest.max_stack == 32
+    hit_gpu, _, _, _ = r.trace_closest(ori, dirs)
+    assert np.array_equal(hit_gpu, hit_cpu)
+    r.render(1)
+    rep = par.compare_staged_frame(ref, r, 2, ref.meta["trace_depth"])
+    assert rep["ok"], par.failures(rep)
+    dn, inn = r.accumulators()
+    assert par.count_bit_mismatch(dn, ref.load("direct", "<f4", 3)) == 0 and par.count_bit_mismatch(inn, ref.load("indirect", "<f4", 3)) == 0
+    assert dn.max() > 0
+    r.free()
+    # every scheduler / node format of the extension rays must fall back to the reference-order walk on such a tree
+    base = (dn, inn)
+    for env in ({"PTB_RC_MODE": "2", "PTB_RC_MINB": "8", "PTB_RC_REFILL": "16"}, {"PTB_RC_MODE": "1", "PTB_RC_REFILL": "24", "PTB_RC_STEPS": "4"}, {"PTB_WIDE": "3"}):
+        got = _render_with(env, lambda: ptb.Renderer(s))
+        assert _bits(got[0], base[0]) and _bits(got[1], base[1]), env
+    mref, cnt = _mega_ref(scene_json, str(tmp_path / "mref"), 2)
+    m = ptb.Renderer(s, megakernel=True)
+    m.render(1, 2)
+    assert par.count_bit_mismatch(m.accumulators()[0], mref) == 0
+    m.free()
+
+
+def test_stress_10m_vs_reference(tmp_path):
+    """BASELINE config[3] against the reference ITSELF: the 10,000,000-triangle scene written as OBJ files, loaded by the
+    reference's own loader and by this one, LBVH built by both (depth 35 > the 32-entry stack), 2 spp at 1920x1080.
+    LBVH arrays are compared through position-weighted checksums (refdump --sums; dumping them would be 1.4 GB), the
+    accumulators bit for bit."""
+    _need_ref()
+    import json as _json
+    import shutil
+    d_scene, d_ref = str(tmp_path / "stress"), str(tmp_path / "ref")
+    scene_json, ntri = scenegen.stress_scene(d_scene, 10_000_000, res=(1920, 1080))
+    try:
+        log = par.run_refdump(scene_json, d_ref, iters=2, stages=False, extra=("--no-dump", "--sums"), timeout=1500)
+        sums = _json.loads([l for l in log.splitlines() if l.startswith("REFSUMS")][0][len("REFSUMS "):])
+        s = ptb.Scene(scene_json)
+        assert s.info.num_triangles == sums["num_triangles"] == ntri and s.info.num_vertices == sums["num_vertices"]
+        assert par.word_sum(s.array("pos")) == sums["pos"] and par.word_sum(s.array("indices_matid")) == sums["indices_matid"]
+        r = ptb.Renderer(s)
+        assert r.stats().lbvh_max_depth > 32
+        for name in ("aabb_min", "aabb_max", "centroid", "primitive_indices", "morton_codes", "child_nodes", "parent", "escape_indices"):
+            assert par.word_sum(r.lbvh(name)) == sums[name], name
+        r.render(1, 2)
+        dn, inn = r.accumulators()
+        rd = np.fromfile(os.path.join(d_ref, "direct.bin"), dtype="<f4").reshape(-1, 3)
+        ri = np.fromfile(os.path.join(d_ref, "indirect.bin"), dtype="<f4").reshape(-1, 3)
+        rr = par.radiance_report(rd, ri, dn, inn, 2)
+        assert rr["max_rel_err"] <= 1e-4 and rr["rmse"] <= 1e-3, rr       # north_star tolerance
+        assert rr["bit_mismatch_direct"] == 0 and rr["bit_mismatch_indirect"] == 0, rr
+        assert dn.max() > 0 and inn.max() > 0
+        r.free(); s.free()
+    finally:
+        shutil.rmtree(d_scene, ignore_errors=True)
+
+
+# ------------------------------------------------------------------------------------------ the reference-side shim
+@pytest.mark.parametrize("which,mode", [("cornell", "file"), ("cornell", "live"), ("fire_small", "live"), ("sponza_small", "file"), ("sponza_small", "live")])
+def test_shim_vs_reference(which, mode, fire_small, sponza_small, tmp_path):
+    """The source-level drop-in: shim/pathtrace_wavefront_ptb200.cpp compiled against the reference's UNCHANGED headers and driven
+    by a copy of its headless loop (shim/shim_driver.cpp: Scene(file) -> PathtraceInit -> Pathtrace(pbo, 0, 1..n) ->
+    PathtraceFree) must leave the accumulators, and the RGBA8 image in the caller's device buffer, that the reference's own
+    pathtrace_wavefront.cu leaves.  "live" hands the scene over from the reference's Scene object (arrays, textures read back
+    from its CUDA arrays, alias table); "file" re-parses the scene file."""
+    _need_ref()
+    if not os.path.exists(par.SHIMDUMP):
+        pytest.skip("oracle/_ref/shimdump not present")
+    scene_json = {"cornell": lambda: scenegen.cornell(str(tmp_path / "c"), res=(200, 160)), "fire_small": lambda: fire_small,
+                  "sponza_small": lambda: sponza_small}[which]()
+    d = str(tmp_path / "ref")
+    par.run_refdump(scene_json, d, iters=3, stages=False, views=True)
+    ref = par.RefDump(d)
+    sd, si, px = par.run_shimdump(scene_json, str(tmp_path / "shim"), 3, mode=mode)
+    assert par.count_bit_mismatch(sd, ref.load("direct", "<f4", 3)) == 0
+    assert par.count_bit_mismatch(si, ref.load("indirect", "<f4", 3)) == 0
+    assert np.array_equal(px, ref.load("view0", "u1", 4))
+
+
 # ------------------------------------------------------------------------------------------ headless views
 @pytest.mark.parametrize("which,iters", [("cornell", 1), ("sponza_small", 1), ("sponza_small", 2)])
 def test_gbuffer_views_and_heatmap_vs_reference(which, iters, sponza_small, tmp_path):
@@ -391,6 +490,27 @@ def test_sample_environment_vs_oracle(tmp_path):
     hist = np.bincount(t, minlength=i.env_width * i.env_height).astype(np.float64)
     row = hist.reshape(i.env_height, i.env_width).sum(axis=1)
     assert row.argmax() < i.env_height // 2      # the sun is in the upper hemisphere
+    r.free(); scene.free()
+
+
+@pytest.mark.gpu
+def test_sample_environment_vs_reference(tmp_path):
+    """ptb_sample_environment against the reference's OWN sampleEnvironmentMap (src/interactions.cu:447-488; defined there,
+    called by nothing) run on the device by refdump --sample-env over the same random pairs: direction and pdf bit for bit."""
+    _need_ref()
+    path = scenegen.sponza(str(tmp_path / "sp"), res=(64, 36), scale=0.05, tex_size=32)[0]
+    scene = ptb.Scene(path)
+    r = ptb.Renderer(scene)
+    rng = np.random.RandomState(9)
+    rnd = rng.random_sample((300000, 2)).astype(np.float32)
+    rnd[:4, 0] = [0.0, np.float32(1.0) - np.float32(2.0 ** -24), 0.5, 1.0]
+    rnd.tofile(str(tmp_path / "rnd.bin"))
+    par.run_refdump(path, str(tmp_path / "ref"), stages=False, extra=("--sample-env", str(tmp_path / "rnd.bin")))
+    rd = np.fromfile(str(tmp_path / "ref" / "env_dir.bin"), dtype="<f4").reshape(-1, 3)
+    rp = np.fromfile(str(tmp_path / "ref" / "env_pdf.bin"), dtype="<f4")
+    d, p, t = r.sample_environment(rnd)
+    assert _bits(p, rp)
+    assert _bits(d, rd)
     r.free(); scene.free()
 
 
@@ -557,3 +677,94 @@ def test_ragged_resolution_and_depth_vs_reference(res, depth, tmp_path):
     m.render(1, 2)
     assert par.count_bit_mismatch(m.accumulators()[0], mref) == 0
     m.free()
+
+
+# ---- multi-GPU inside the C ABI: peer-store gather, hybrid tile x sample partition (include/ptb200.h "multi-GPU") -------
+def _devices(n):
+    have = capi.lib.ptb_device_count()
+    return [k % have for k in range(n)]          # one GPU: the renderers share it (the gather is then a local store)
+
+
+@pytest.mark.gpu
+def test_multi_renderer_tile_and_hybrid(fire_small):
+    """ptb_multi_* through ctypes only (no torch in this path): a frame cut into 4 stripe sets is bit-identical to one renderer
+    in every output format; 2 tile groups x 2 sample groups agree with one renderer's 4 spp to summation order, twice the same
+    bits; the no-P2P copy route gives the peer-store route's bits."""
+    s = ptb.Scene(fire_small)
+    one = ptb.Renderer(s)
+    one.render(1, 3)
+    ref_sum, ref_mean, ref_rgba = one.resolve(3, capi.IMG_SUM_RGB32F), one.resolve(3), one.resolve(3, capi.IMG_RGBA8)
+    m = ptb.MultiRenderer(s, _devices(4))
+    assert (m.tile_groups, m.sample_groups) == (4, 1)
+    m.render(1, 3)
+    assert _bits(m.resolve(capi.IMG_SUM_RGB32F), ref_sum)
+    assert _bits(m.resolve(capi.IMG_MEAN_RGB32F), ref_mean)
+    assert np.array_equal(m.resolve(capi.IMG_RGBA8), ref_rgba)
+    info = m.info
+    assert info.samples == 3 and info.n_devices == 4 and info.peer_stores == 4
+    assert sum(m.stats(k).extension_rays for k in range(4)) == one.stats().extension_rays
+    m.render(1, 1)                                  # step 1 restarts the accumulation
+    one.render(1, 1)
+    assert _bits(m.resolve(capi.IMG_SUM_RGB32F), one.resolve(1, capi.IMG_SUM_RGB32F))
+    m.free()
+    one.render(1, 4)
+    ref4 = one.resolve(4, capi.IMG_SUM_RGB32F)
+    h = ptb.MultiRenderer(s, _devices(4), tile_groups=2)
+    assert (h.tile_groups, h.sample_groups) == (2, 2)
+    h.render(1, 2)                                  # 2 steps x 2 sample groups = iterations 1..4
+    a = h.resolve(capi.IMG_SUM_RGB32F)
+    err = np.abs(a - ref4) / np.maximum(np.abs(ref4), 1e-3)
+    assert err.max() <= 1e-5, err.max()
+    h.render(1, 2)
+    assert _bits(h.resolve(capi.IMG_SUM_RGB32F), a)
+    assert h.info.samples == 4
+    h.free()
+    os.environ["PTB_MULTI_NO_P2P"] = "1"
+    try:
+        c = ptb.MultiRenderer(s, _devices(4), tile_groups=2)
+        c.render(1, 2)
+        assert c.info.peer_stores == 1              # only the root itself
+        assert _bits(c.resolve(capi.IMG_SUM_RGB32F), a)
+        c.free()
+    finally:
+        del os.environ["PTB_MULTI_NO_P2P"]
+    with pytest.raises(capi.PtbError):
+        ptb.MultiRenderer(s, _devices(4), tile_groups=3)
+    one.free(); s.free()
+
+
+_IPC_CHILD = """
+import sys
+sys.path.insert(0, {root!r})
+import cuda_path_tracer_b200 as ptb
+s = ptb.Scene({scene!r})
+r = ptb.Renderer(s, rank=1, world=2, stripe_rows=8)
+r.render(1, 2); 
+g = ptb.Gather.open(0, bytes.fromhex({handle!r}), r.width, r.height, 1)
+g.resolve_from(r, 0)
+r.sync()
+print("CHILD_OK")
+g.free(); r.free()
+"""
+
+
+@pytest.mark.gpu
+def test_gather_across_processes_ipc(fire_small):
+    """One process per GPU: the root exports its frame buffer (ptb_gather_export, a CUDA IPC handle), another PROCESS opens it
+    and its resolve kernel stores its stripes into the root's memory; the combined frame is the one-renderer frame, bit for bit."""
+    import subprocess
+    import sys
+    s = ptb.Scene(fire_small)
+    one = ptb.Renderer(s)
+    one.render(1, 2)
+    ref = one.resolve(2)
+    r0 = ptb.Renderer(s, rank=0, world=2, stripe_rows=8)
+    g = ptb.Gather(0, r0.width, r0.height, 1)
+    code = _IPC_CHILD.format(root=os.path.dirname(os.path.dirname(os.path.abspath(__file__))), scene=fire_small, handle=g.export().hex())
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert "CHILD_OK" in p.stdout, p.stdout[-1000:] + p.stderr[-2000:]
+    r0.render(1, 2)
+    g.resolve_from(r0, 0)
+    r0.sync()
+    assert _bits(g.combine(2), ref)
+    g.free(); r0.free(); one.free(); s.free()
