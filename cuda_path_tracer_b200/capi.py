@@ -72,6 +72,7 @@ class MultiInfo(C.Structure):  # ptb_multi_info
 
 
 GATHER_HANDLE_BYTES = 64
+NOALLOC_MAX_RAYS = 262144
 
 
 class Stats(C.Structure):
@@ -118,6 +119,7 @@ SIGNATURES = {
     "ptb_build_lbvh": (C.c_int, [C.c_int32, P, C.c_int32, P, C.c_int32, P, P, P, P, P, P, P, P, P]),
     "ptb_trace_closest": (C.c_int, [P, P, P, C.c_int32, P, P, P, P]),
     "ptb_trace_occluded": (C.c_int, [P, P, P, C.c_int32, P]),
+    "ptb_trace_closest_noalloc": (C.c_int, [P, P, P, C.c_int32, P, P, P, P]),
     "ptb_stage_run": (C.c_int, [P, C.c_int32, C.c_int32]),
     "ptb_get_queue_count": (C.c_int, [P, C.c_int32, C.POINTER(C.c_int32)]),
     "ptb_get_queue": (C.c_int, [P, C.c_int32, P, C.c_int32]),

@@ -76,6 +76,7 @@ const ptb::FrameDev& ptb_internal_frame(const ptb_renderer* r) { return r->frame
 int ptb_internal_device(const ptb_renderer* r) { return r->device; }
 cudaStream_t ptb_internal_stream(const ptb_renderer* r) { return r->stream; }
 void ptb_internal_count_launches(ptb_renderer* r, int n) { r->kernel_launches += n; }
+int ptb_internal_num_sms(const ptb_renderer* r) { return r->launch.num_sms; }
 
 template <typename T>
 static int dev_alloc(ptb_renderer* r, T*& p, size_t count) {

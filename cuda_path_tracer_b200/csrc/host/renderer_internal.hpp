@@ -9,3 +9,4 @@ const ptb::FrameDev& ptb_internal_frame(const ptb_renderer* r);
 int ptb_internal_device(const ptb_renderer* r);
 cudaStream_t ptb_internal_stream(const ptb_renderer* r);
 void ptb_internal_count_launches(ptb_renderer* r, int n);
+int ptb_internal_num_sms(const ptb_renderer* r);

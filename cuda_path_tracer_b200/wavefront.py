@@ -235,6 +235,16 @@ class Renderer:
         check(lib.ptb_trace_closest(self._h, ptr(ori4), ptr(dir4), n, ptr(hit), ptr(t), ptr(u), ptr(v)))
         return hit, t, u, v
 
+    def trace_closest_noalloc(self, ori4, dir4):
+        """trace_closest through ptb_trace_closest_noalloc: static device scratch, at most capi.NOALLOC_MAX_RAYS rays."""
+        ori4 = np.ascontiguousarray(ori4, dtype=np.float32).reshape(-1, 4)
+        dir4 = np.ascontiguousarray(dir4, dtype=np.float32).reshape(-1, 4)
+        n = ori4.shape[0]
+        hit = np.empty(n, dtype=np.int32)
+        t, u, v = (np.empty(n, dtype=np.float32) for _ in range(3))
+        check(lib.ptb_trace_closest_noalloc(self._h, ptr(ori4), ptr(dir4), n, ptr(hit), ptr(t), ptr(u), ptr(v)))
+        return hit, t, u, v
+
     def trace_occluded(self, ori_tmax4, dir4):
         ori_tmax4 = np.ascontiguousarray(ori_tmax4, dtype=np.float32).reshape(-1, 4)
         dir4 = np.ascontiguousarray(dir4, dtype=np.float32).reshape(-1, 4)

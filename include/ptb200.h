@@ -339,6 +339,20 @@ int ptb_trace_closest(ptb_renderer* r, const float* ori4, const float* dir4, int
 int ptb_trace_occluded(ptb_renderer* r, const float* ori_tmax4, const float* dir4, int32_t n,
                        int32_t* occluded);
 
+/* ptb_trace_closest for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same arguments and
+ * results as ptb_trace_closest (host arrays in, host arrays out, synchronous), but the staged rays, the staged results and the
+ * kernel's work cursor live in ONE file-scope static __device__ array (csrc/host/noalloc.cu) instead of a cudaMalloc'ed scratch
+ * buffer, and the call makes no cudaMalloc / cudaFree / event creation or any other allocating call.
+ *   - n > PTB_NOALLOC_MAX_RAYS is rejected with PTB_ERR_INVALID (split the batch, or use ptb_trace_closest);
+ *   - the array is PTB_NOALLOC_MAX_RAYS * 48 B + 256 B (12 MB) and every GPU that loads the library holds it until exit;
+ *   - all calls on a GPU share it and it keeps the previous call's contents (the cursor is cleared per call): calls that
+ *     overlap on the same GPU race -- serialise them;
+ *   - ptb_stats.last_batch_ms is not updated (timing would need events). */
+#define PTB_NOALLOC_MAX_RAYS 262144
+int ptb_trace_closest_noalloc(ptb_renderer* r, const float* ori4, const float* dir4, int32_t n,
+                              int32_t* hit_geom_id, float* t, float* u, float* v);
+
 /* ---------------------------------------------- staged frame (parity/debug) */
 /* The reference's stage wrappers driven one at a time, in the order of
  * src/pathtrace_wavefront.cu:278-348, so that tests can read queues between stages. */
