@@ -54,7 +54,11 @@ __device__ __forceinline__ int logic_path(const FrameDev& f, int idx, int hit, i
     if (hit == -1) {
         if (f.tex.env_tex_id >= 0) {
             float4 dd = HAVE_RAY ? dd_in : f.pool.ray_dir_dist[idx];
-            Vec3 dir = normalize3(Vec3(dd.x, dd.y, dd.z));
+            // normalize with the dot product's contraction PINNED to the reference's fma(z,z, fma(x,x, y*y)): left to nvcc it depends on
+            // the kernel this function is inlined into (the 4-wide persistent-lane kernel got fma(z,z, fma(y,y, x*x)), which moves the
+            // environment lookup by an ulp and the filtered texel with it: 168 pixels of the textured scene's indirect image)
+            const Vec3 dv(dd.x, dd.y, dd.z);
+            Vec3 dir = dv * (1.0f / sqrtf(dot3_pinned(dv, dv)));
             float phi = atan2f(dir.z, dir.x);
             if (phi < 0) phi += PTB_TWO_PI;
             float theta = acosf(clampf(dir.y, -1.0f, 1.0f));

@@ -169,6 +169,63 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_
     }
 }
 
+// Visibility rays with persistent lanes (the scheduler of k_trace_extension_pl) on the 4-wide quantised tree; trees up to 32
+// levels deep (the stack column is PTB_EXT_STACK entries).  A ray the wide walk cannot decide is re-walked on the fp32 records.
+template <int MINB, int STEPS>
+__global__ void __launch_bounds__(PTB_RC_THREADS, MINB) k_trace_shadow_pl(FrameDev f, int bounce, int refill) {
+    __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
+    int* ctr = f.ctr + bounce * CTR_STRIDE;
+    const int count = ctr[CTR_SHADOW];
+    int* cursor = &ctr[CTR_WORK_SHADOW];
+    StackShared st(stack + threadIdx.x);
+    const unsigned lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    int ray = -1;
+    WalkAnyWide w;
+    w.reset();
+    bool exhausted = false;
+    for (;;) {
+        const unsigned idle_mask = __ballot_sync(0xffffffffu, ray < 0);
+        const int n_idle = __popc(idle_mask);
+        if (exhausted && n_idle == 32) break;
+        if (!exhausted && n_idle >= refill) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(cursor, n_idle);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            exhausted = base + n_idle >= count;
+            const int i = base + __popc(idle_mask & lt);
+            if (ray < 0 && i < count) {
+                ray = i;
+                float4 o4 = __ldg(&f.shadow.ray_ori_tmax[i]);
+                float4 d4 = __ldg(&f.shadow.ray_dir[i]);
+                w.init(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), o4.w);
+            }
+        }
+        const int want = exhausted ? 32 : refill;
+        int n_done;
+        do {
+#pragma unroll
+            for (int k = 0; k < STEPS; k++)
+                if (w.busy()) w.step(f.bvh, st);
+            n_done = __popc(__ballot_sync(0xffffffffu, !w.busy()));
+        } while (n_done < want);
+        if (ray >= 0 && !w.busy()) {
+            int res = w.result;
+            if (res < 0) res = trace_any<PTB_EXT_STACK>(f.bvh, w.r.o, w.r.d, w.tmax, st.col, PTB_RC_THREADS);
+            if (res == 0) {   // visible: AtomicAddVec3(&d_direct_image[pixel], radiance), src/kernels/ray_cast.cu:193-199
+                int slot = __ldg(&f.shadow.slot[ray]);
+                float4 rad = __ldg(&f.shadow.radiance[ray]);
+                float* dst = f.direct + 3 * (size_t)slot;
+                atomicAdd(dst + 0, rad.x);
+                atomicAdd(dst + 1, rad.y);
+                atomicAdd(dst + 2, rad.z);
+            } else if (res < 0) {
+                atomicExch(f.error_flag, 1);
+            }
+            ray = -1;
+        }
+    }
+}
+
 static inline int rc_grid(const LaunchCfg& c) { return c.num_sms * (c.rc_blocks > 0 ? c.rc_blocks : 8); }
 
 template <class WALK, class STACK, int MINB, int STEPS = 1>
@@ -182,19 +239,19 @@ static void run_extension_pl(const FrameDev& f, int bounce, int* cursor, const L
 static void run_extension(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c_in, cudaStream_t s, bool fuse_logic = false) {
     LaunchCfg c = c_in;
     if (bounce == 0 && !c.rc_b0) c.rc_mode = 0;      // primary rays are coherent and of equal length: one batch per fetch is the best schedule
-    // rc_mode: 0 = one batch per fetch on the fp32 records (below); 1 = persistent lanes, fp32 records; 2 = persistent lanes,
-    // 32-byte quantised records.  rc_stack: 1 = hybrid stack (8 entries in shared memory, the rest local).  rc_minb: resident
-    // blocks per SM the kernel is built and launched for (10: 48 registers, 9: 56, 8: 64).
-    if (c.rc_mode == 1 && c.rc_steps == 2) return run_extension_pl<WalkBinary, StackShared, 10, 2>(f, bounce, cursor, c, s, fuse_logic);
-    if (c.rc_mode == 1 && c.rc_steps == 4) return run_extension_pl<WalkBinary, StackShared, 10, 4>(f, bounce, cursor, c, s, fuse_logic);
-    if (c.rc_mode == 1 || c.rc_mode == 2) {
-#define PTB_PL(W, S, B) return run_extension_pl<W, S, B>(f, bounce, cursor, c, s, fuse_logic)
-#define PTB_PL_B(W, S) do { if (c.rc_minb == 8) PTB_PL(W, S, 8); if (c.rc_minb == 9) PTB_PL(W, S, 9); PTB_PL(W, S, 10); } while (0)
-        if (c.rc_mode == 1) { if (c.rc_stack) PTB_PL_B(WalkBinary, StackHybrid<8>); else PTB_PL_B(WalkBinary, StackShared); }
-        else { if (c.rc_stack) PTB_PL_B(WalkBq, StackHybrid<8>); else PTB_PL_B(WalkBq, StackShared); }
+    // rc_mode: 0 = one batch per fetch on the fp32 records (below); persistent lanes on 1 = the fp32 records, 2 = the 32-byte
+    // quantised binary records, 3 = the 4-wide quantised records.  rc_stack: 1 = hybrid stack (8 entries in shared memory,
+    // the rest local).  rc_minb: resident blocks per SM the kernel is built and launched for (10: 48 registers, 9: 56, 8: 64).
+    // rc_steps: traversal steps between two ballots.
+#define PTB_PL(W, S, B, T) return run_extension_pl<W, S, B, T>(f, bounce, cursor, c, s, fuse_logic)
+#define PTB_PL_T(W, S, B) do { if (c.rc_steps >= 8) PTB_PL(W, S, B, 8); if (c.rc_steps >= 4) PTB_PL(W, S, B, 4); if (c.rc_steps >= 2) PTB_PL(W, S, B, 2); PTB_PL(W, S, B, 1); } while (0)
+#define PTB_PL_B(W, S) do { if (c.rc_minb == 8) PTB_PL_T(W, S, 8); if (c.rc_minb == 9) PTB_PL_T(W, S, 9); PTB_PL_T(W, S, 10); } while (0)
+    if (c.rc_mode == 1) { if (c.rc_stack) PTB_PL_B(WalkBinary, StackHybrid<8>); else PTB_PL_B(WalkBinary, StackShared); }
+    if (c.rc_mode == 2) { if (c.rc_stack) PTB_PL_B(WalkBq, StackHybrid<8>); else PTB_PL_B(WalkBq, StackShared); }
+    if (c.rc_mode == 3) PTB_PL_B(WalkWide, StackShared);
 #undef PTB_PL_B
+#undef PTB_PL_T
 #undef PTB_PL
-    }
     const bool wide = (c.wide & 2) != 0;
     if (fuse_logic && wide) k_trace_extension<true, true><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
     else if (fuse_logic) k_trace_extension<true, false><<<rc_grid(c), PTB_RC_THREADS, 0, s>>>(f, bounce, cursor);
@@ -217,6 +274,17 @@ int launch_trace_shadow(const FrameDev& f, int bounce, const LaunchCfg& c, cudaS
     // the DFS stack never holds more than one entry per tree level: size it from the measured LBVH depth
     const int g = rc_grid(c);
     const bool wide = (c.wide & 1) != 0;
+    if (c.shadow_deep == 0 && wide && c.sh_mode == 1) {
+        const int refill = c.sh_refill < 1 ? 32 : c.sh_refill > 32 ? 32 : c.sh_refill;
+#define PTB_SPL(B, T) do { k_trace_shadow_pl<B, T><<<c.num_sms * B, PTB_RC_THREADS, 0, s>>>(f, bounce, refill); return 1; } while (0)
+#define PTB_SPL_T(B) do { if (c.sh_steps >= 8) PTB_SPL(B, 8); if (c.sh_steps >= 4) PTB_SPL(B, 4); if (c.sh_steps >= 2) PTB_SPL(B, 2); PTB_SPL(B, 1); } while (0)
+        if (c.sh_minb >= 12) PTB_SPL_T(12);
+        if (c.sh_minb == 8) PTB_SPL_T(8);
+        if (c.sh_minb == 9) PTB_SPL_T(9);
+        PTB_SPL_T(10);
+#undef PTB_SPL_T
+#undef PTB_SPL
+    }
     if (c.shadow_deep == 3) k_trace_shadow<256, false, false><<<g, PTB_RC_THREADS, 0, s>>>(f, bounce);
     else if (c.shadow_deep == 0 && wide) k_trace_shadow<32, true, true><<<c.num_sms * (c.sh_blocks > 0 ? c.sh_blocks : PTB_SH_MINBLOCKS), PTB_RC_THREADS, 0, s>>>(f, bounce);
     else if (c.shadow_deep == 0) k_trace_shadow<32, true, false><<<c.num_sms * PTB_SH_MINBLOCKS, PTB_RC_THREADS, 0, s>>>(f, bounce);

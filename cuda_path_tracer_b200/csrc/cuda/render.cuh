@@ -65,6 +65,8 @@ struct LaunchCfg {
     int overlap_shadow;       // frame graph: TraceShadow(b) runs beside TraceExtension(b) on a forked branch
     int wide;                 // 4-wide quantised traversal (wide.cuh): bit 0 shadow rays, bit 1 extension rays, bit 2 megakernel
     int sh_blocks;            // resident blocks per SM of the wide shadow kernel
+    int sh_mode, sh_refill, sh_steps, sh_minb;   // shadow rays: 1 = persistent lanes (k_trace_shadow_pl), refill threshold, steps per ballot, blocks per SM
+    int shade_fork;           // frame graph: the four material kernels of a bounce run as parallel branches
     int rc_mode;              // extension-ray scheduler / node format (raycast.cu run_extension)
     int rc_stack, rc_minb, rc_steps, rc_b0;    // see raycast.cu run_extension
     int rc_refill;            // persistent lanes: idle lanes per warp that trigger a refill (32 = one batch per fetch)
@@ -85,6 +87,7 @@ int launch_trace_shadow(const FrameDev& f, int bounce, const LaunchCfg& c, cudaS
 int launch_trace_extension_only(const FrameDev& f, int bounce, int* cursor, const LaunchCfg& c, cudaStream_t s);
 int launch_logic(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
 int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t s);
+int launch_shade_one(const FrameDev& f, int bounce, int type, const LaunchCfg& c, cudaStream_t s);   // type: MAT_*
 int launch_fold_env(const FrameDev& f, cudaStream_t s);
 int launch_sample_environment(const FrameDev& f, const float* rnd, int n, float* dir, float* pdf, int* pixel, cudaStream_t s);
 // ptb_config.megakernel (megakernel.cu): counters reset + the whole frame in one kernel

@@ -347,6 +347,18 @@ int launch_shade(const FrameDev& f, int bounce, const LaunchCfg& c, cudaStream_t
     k_shade<MAT_REFRACT, false><<<stage_grid(c), kThreads, 0, s>>>(f, bounce);
     return 4;
 }
+// One material queue's kernel on its own stream: the four queues hold disjoint paths and only share the (atomic) counters of
+// the next bounce, so the frame graph runs them as parallel branches (renderer.cu, LaunchCfg::shade_fork).
+int launch_shade_one(const FrameDev& f, int bounce, int type, const LaunchCfg& c, cudaStream_t s) {
+    const int g = stage_grid(c);
+    switch (type) {
+        case MAT_PBR: if (f.env.nee) k_shade<MAT_PBR, true><<<g, kThreads, 0, s>>>(f, bounce); else k_shade<MAT_PBR, false><<<g, kThreads, 0, s>>>(f, bounce); break;
+        case MAT_DIFFUSE: if (f.env.nee) k_shade<MAT_DIFFUSE, true><<<g, kThreads, 0, s>>>(f, bounce); else k_shade<MAT_DIFFUSE, false><<<g, kThreads, 0, s>>>(f, bounce); break;
+        case MAT_REFLECT: k_shade<MAT_REFLECT, false><<<g, kThreads, 0, s>>>(f, bounce); break;
+        default: k_shade<MAT_REFRACT, false><<<g, kThreads, 0, s>>>(f, bounce); break;
+    }
+    return 1;
+}
 // ptb_config.env_nee: the environment's shadow rays accumulate into direct[P .. 2P) so that every accumulator cell
 // still receives at most one add per bounce (a deterministic sum, bit-identical between the tile partitions); the
 // frame ends by folding that half into the direct image.

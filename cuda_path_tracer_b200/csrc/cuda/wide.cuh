@@ -346,6 +346,141 @@ struct WalkBq {
     }
 };
 
+// WalkWide: trace_closest_wide() cut at the loop body (closest hit on the 4-wide quantised tree, nearest child first); a result
+// that could depend on the reference's visiting order is re-traced in that order by finish(), as trace_closest_exact() does.
+struct WalkWide {
+    WideRay r;
+    float t, u, v, second;                    // best hit (t = FLT_MAX: none), nearest other accepted candidate
+    int leaf;
+    int node, sp;
+    bool bad;
+    __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
+    __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
+    __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o, Vec3 d) {
+        r = wide_setup(bvh, o, d);
+        t = FLT_MAX; u = 0.0f; v = 0.0f; second = FLT_MAX; leaf = -1;
+        sp = 0;
+        bad = !r.ok;
+        node = bad ? PTB_NODE_NONE : 0;
+    }
+    template <class STACK>
+    __device__ __forceinline__ void step(const BvhDev& bvh, STACK& st) {
+        if (node == PTB_NODE_NONE) node = st.get(--sp);
+        const float limit = t * PTB_WIDE_SLACK;
+        if (node >= 0) {
+            const uint4* np = bvh.wnode + 4 * (size_t)node;
+            F8 a = ldg256(reinterpret_cast<const float4*>(np)), b = ldg256(reinterpret_cast<const float4*>(np + 2));
+            const uint4 qx = make_uint4(__float_as_uint(a.a.x), __float_as_uint(a.a.y), __float_as_uint(a.a.z), __float_as_uint(a.a.w));
+            const uint4 qy = make_uint4(__float_as_uint(a.b.x), __float_as_uint(a.b.y), __float_as_uint(a.b.z), __float_as_uint(a.b.w));
+            const uint4 qz = make_uint4(__float_as_uint(b.a.x), __float_as_uint(b.a.y), __float_as_uint(b.a.z), __float_as_uint(b.a.w));
+            int lnk[4] = {__float_as_int(b.b.x), __float_as_int(b.b.y), __float_as_int(b.b.z), __float_as_int(b.b.w)};
+            float key[4];
+            wide_test(r, qx, qy, qz, limit, key);
+#pragma unroll
+            for (int k = 0; k < 4; k++) if (key[k] < 0.0f) key[k] = FLT_MAX;     // misses sort last
+            PTB_WIDE_CSWAP(0, 1) PTB_WIDE_CSWAP(2, 3) PTB_WIDE_CSWAP(0, 2) PTB_WIDE_CSWAP(1, 3) PTB_WIDE_CSWAP(1, 2)
+#pragma unroll
+            for (int k = 3; k >= 1; k--) {
+                if (key[k] != FLT_MAX) {
+                    if (sp < PTB_WIDE_STACK) st.set(sp++, lnk[k]);
+                    else bad = true;
+                }
+            }
+            node = (key[0] != FLT_MAX) ? lnk[0] : PTB_NODE_NONE;
+        } else {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
+            float tu, tv;
+            float tt = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), r.o, r.d, tu, tv);
+            if (tt > PTB_EPSILON && tt < limit) {
+                float tb = leaf_box_test(a, b, c, r.o, r.inv);
+                if (tb != -1.0f && tb < limit) {
+                    if (tt < t && tb < t) {                          // the reference's acceptance, src/kernels/ray_cast.cu:68,93-94
+                        second = fminf(second, t);
+                        t = tt; u = tu; v = tv;
+                        leaf = ~node;
+                    } else {
+                        second = fminf(second, tt);
+                    }
+                }
+            }
+            node = PTB_NODE_NONE;
+        }
+        if (bad) { node = PTB_NODE_NONE; sp = 0; }
+    }
+    template <class STACK>
+    __device__ __forceinline__ Hit finish(const BvhDev& bvh, STACK& st) {
+        const bool ambiguous = bad || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
+        if (ambiguous) {
+            WalkBinary w;
+            w.init(bvh, r.o, r.d);
+            while (w.busy()) w.step(bvh, st);
+            return w.h;
+        }
+        Hit h;
+        h.prim = -1; h.mat = -1; h.t = t; h.u = u; h.v = v;
+        if (leaf >= 0) {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)leaf;
+            h.prim = __float_as_int(__ldg(tp).w);
+            h.mat = __float_as_int(__ldg(tp + 1).w);
+        }
+        return h;
+    }
+};
+
+// WalkAnyWide: trace_any_wide() cut at the loop body (visibility rays on the 4-wide quantised tree), for the persistent-lane
+// shadow kernel.  result: 0 nothing found (so far), 1 occluded, -1 not decidable here -> finish() takes the binary walk.
+struct WalkAnyWide {
+    WideRay r;
+    float tmax;
+    int node, sp, result;
+    __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
+    __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
+    __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o, Vec3 d, float tmax_) {
+        r = wide_setup(bvh, o, d);
+        tmax = tmax_;
+        sp = 0;
+        result = r.ok ? 0 : -1;
+        node = r.ok ? 0 : PTB_NODE_NONE;
+    }
+    template <class STACK>
+    __device__ __forceinline__ void step(const BvhDev& bvh, STACK& st) {
+        if (node == PTB_NODE_NONE) node = st.get(--sp);
+        if (node >= 0) {
+            const uint4* np = bvh.wnode + 4 * (size_t)node;
+            F8 a = ldg256(reinterpret_cast<const float4*>(np)), b = ldg256(reinterpret_cast<const float4*>(np + 2));
+            const uint4 qx = make_uint4(__float_as_uint(a.a.x), __float_as_uint(a.a.y), __float_as_uint(a.a.z), __float_as_uint(a.a.w));
+            const uint4 qy = make_uint4(__float_as_uint(a.b.x), __float_as_uint(a.b.y), __float_as_uint(a.b.z), __float_as_uint(a.b.w));
+            const uint4 qz = make_uint4(__float_as_uint(b.a.x), __float_as_uint(b.a.y), __float_as_uint(b.a.z), __float_as_uint(b.a.w));
+            const int lnk[4] = {__float_as_int(b.b.x), __float_as_int(b.b.y), __float_as_int(b.b.z), __float_as_int(b.b.w)};
+            float t[4];
+            wide_test(r, qx, qy, qz, tmax, t);
+            node = PTB_NODE_NONE;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (t[k] >= 0.0f) {
+                    if (node == PTB_NODE_NONE) node = lnk[k];
+                    else if (sp < PTB_WIDE_STACK) st.set(sp++, lnk[k]);
+                    else result = -1;
+                }
+            }
+        } else {
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
+            F8 ab = ldg256(tp);
+            float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
+            float u, v;
+            float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), r.o, r.d, u, v);
+            node = PTB_NODE_NONE;
+            if (t > PTB_EPSILON && t < __fsub_rn(tmax, PTB_EPSILON)) {
+                float tb = leaf_box_test(a, b, c, r.o, r.inv);          // the reference reaches this leaf iff its own box passes
+                if (tb != -1.0f && tmax > tb) result = 1;
+            }
+        }
+        if (result != 0) { node = PTB_NODE_NONE; sp = 0; }
+    }
+};
+
 // The two walks behind one call: wide first, the reference-order binary walk where the wide one cannot vouch for the result.
 __device__ __forceinline__ Hit trace_closest_exact(const BvhDev& bvh, Vec3 o, Vec3 d, int* stack, int stride) {
     WideRay r = wide_setup(bvh, o, d);

@@ -30,6 +30,8 @@ struct ptb_renderer {
     bool own_stream = false;
     cudaStream_t side = nullptr;          // forked branch of the frame (shadow rays beside extension rays)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t shade_side[3] = {nullptr, nullptr, nullptr};   // forked branches of Shade: PBR, mirror, dielectric beside diffuse
+    cudaEvent_t ev_sfork = nullptr, ev_sjoin[3] = {nullptr, nullptr, nullptr};
     ptb_config cfg{};
 
     // scene replica on the device
@@ -190,7 +192,10 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
     n += launch_raygen(f, r->launch, s);
     for (int b = 0; b < f.trace_depth; b++) {
         // whole frames run Logic inside the extension RayCast kernel; the staged API keeps the stages apart
-        const bool fuse = r->launch.fuse_logic != 0;
+        // Logic in the tail of the RayCast kernel: pays in the batch kernel and in the 64-register persistent-lane kernels (10.4 vs
+        // 11.0 ms per frame), costs spills in the 48-register ones (fuse_logic = 2 keeps it to the batch kernel)
+        const bool batch_kernel = r->launch.rc_mode == 0 || (b == 0 && !r->launch.rc_b0);
+        const bool fuse = r->launch.fuse_logic == 1 || (r->launch.fuse_logic == 2 && batch_kernel);
         if (b > 0 && r->launch.overlap_shadow && r->side) {
             // TraceShadow(b) reads what Shade(b-1) queued and only adds to `direct`; TraceExtension(b) + Logic(b) touch
             // the path pool and `indirect`: independent until Shade(b), so they run as two branches of the graph and
@@ -209,7 +214,21 @@ static int enqueue_frame(ptb_renderer* r, cudaStream_t s) {
         if (b == 0 && r->gbuffer) n += launch_gbuffer(f, r->gb, s);   // the reference's Logic writes it on the first bounce
         // Rays produced by the last Shade are never traced (loop bound src/pathtrace_wavefront.cu:281,
         // counters overwritten by the next RayGen, src/kernels/ray_gen.cu:121-124): skip it.
-        if (b + 1 < f.trace_depth) n += launch_shade(f, b, r->launch, s);
+        if (b + 1 < f.trace_depth) {
+            if (r->launch.shade_fork && r->shade_side[0]) {
+                static const int side_type[3] = {MAT_PBR, MAT_REFLECT, MAT_REFRACT};
+                cudaEventRecord(r->ev_sfork, s);
+                for (int k = 0; k < 3; k++) {
+                    cudaStreamWaitEvent(r->shade_side[k], r->ev_sfork, 0);
+                    n += launch_shade_one(f, b, side_type[k], r->launch, r->shade_side[k]);
+                    cudaEventRecord(r->ev_sjoin[k], r->shade_side[k]);
+                }
+                n += launch_shade_one(f, b, MAT_DIFFUSE, r->launch, s);
+                for (int k = 0; k < 3; k++) cudaStreamWaitEvent(s, r->ev_sjoin[k], 0);
+            } else {
+                n += launch_shade(f, b, r->launch, s);
+            }
+        }
     }
     if (f.env.nee) n += launch_fold_env(f, s);
     if (r->denoiser) n += launch_svgf(f, r->svgf, r->gb, r->launch.num_sms, s);   // reads *f.iteration: before frame_end advances it
@@ -263,6 +282,8 @@ int ptb_free(ptb_renderer* r) {
     if (r->side) cudaStreamDestroy(r->side);
     if (r->ev_fork) cudaEventDestroy(r->ev_fork);
     if (r->ev_join) cudaEventDestroy(r->ev_join);
+    for (int k = 0; k < 3; k++) { if (r->shade_side[k]) cudaStreamDestroy(r->shade_side[k]); if (r->ev_sjoin[k]) cudaEventDestroy(r->ev_sjoin[k]); }
+    if (r->ev_sfork) cudaEventDestroy(r->ev_sfork);
     delete r;
     return PTB_OK;
 }
@@ -300,19 +321,31 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     {   // tuning knobs of the RayCast scheduler (defaults are the measured best; env overrides are for A/B runs only)
         auto knob = [](const char* name, int def) { const char* e = std::getenv(name); return e ? std::atoi(e) : def; };
         r->launch.rc_blocks = knob("PTB_RC_BLOCKS", 10);
-        r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);
+        r->launch.fuse_logic = knob("PTB_FUSE_LOGIC", 1);   // 0 never, 1 every bounce, 2 only where the one-batch-per-fetch kernel runs (bounce 0)
         r->launch.overlap_shadow = knob("PTB_OVERLAP_SHADOW", 1);
         r->launch.wide = knob("PTB_WIDE", 1);
         r->launch.sh_blocks = knob("PTB_SH_BLOCKS", 12);
-        r->launch.rc_mode = knob("PTB_RC_MODE", 0);
-        r->launch.rc_refill = knob("PTB_RC_REFILL", 32);
+        r->launch.sh_mode = knob("PTB_SH_MODE", 1);
+        r->launch.sh_refill = knob("PTB_SH_REFILL", 24);
+        r->launch.sh_steps = knob("PTB_SH_STEPS", 4);
+        r->launch.sh_minb = knob("PTB_SH_MINB", 9);
+        r->launch.rc_mode = knob("PTB_RC_MODE", 3);
+        r->launch.rc_refill = knob("PTB_RC_REFILL", 24);
         r->launch.rc_stack = knob("PTB_RC_STACK", 0);
-        r->launch.rc_minb = knob("PTB_RC_MINB", 10);
-        r->launch.rc_steps = knob("PTB_RC_STEPS", 1);
+        r->launch.rc_minb = knob("PTB_RC_MINB", 8);
+        r->launch.rc_steps = knob("PTB_RC_STEPS", 4);
         r->launch.rc_b0 = knob("PTB_RC_B0", 0);
         r->launch.mega_regen = knob("PTB_MEGA_REGEN", 1);
         r->launch.mega_refill = knob("PTB_MEGA_REFILL", 1);
         r->launch.mega_blocks = knob("PTB_MEGA_BLOCKS", 10);
+        r->launch.shade_fork = knob("PTB_SHADE_FORK", 0);   // measured: no gain (12.26 vs 12.28 ms), the frame is a sum of issue-bound kernels
+        if (r->launch.shade_fork) {
+            for (int k = 0; k < 3; k++) {
+                TRYCU(cudaStreamCreateWithFlags(&r->shade_side[k], cudaStreamNonBlocking));
+                TRYCU(cudaEventCreateWithFlags(&r->ev_sjoin[k], cudaEventDisableTiming));
+            }
+            TRYCU(cudaEventCreateWithFlags(&r->ev_sfork, cudaEventDisableTiming));
+        }
         if (r->launch.overlap_shadow) {
             TRYCU(cudaStreamCreateWithFlags(&r->side, cudaStreamNonBlocking));
             TRYCU(cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming));
@@ -402,7 +435,7 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         // The reference's closest-hit walk gives up once 32 entries are stacked (src/kernels/ray_cast.cu:106), which can only
         // happen in a tree at least 32 levels deep.  The quantised walks visit in another order and would not give up at
         // the same ray, so extension rays of such trees always take the reference-order walk on the fp32 records.
-        if (dmax >= PTB_EXT_STACK_DEPTH) { r->launch.wide &= ~2; if (r->launch.rc_mode == 2) r->launch.rc_mode = 1; }
+        if (dmax >= PTB_EXT_STACK_DEPTH) { r->launch.wide &= ~2; if (r->launch.rc_mode >= 2) r->launch.rc_mode = 1; }
     }
 
     // ---- path pool, queues, accumulators (initWavefrontQueues / initImageSystem,

@@ -24,10 +24,11 @@ for cfg in configs:
     os.environ.update({k: str(v) for k, v in cfg.items()})
     r = ptb.Renderer(scene)
     r.stage(capi.STAGE_RAYGEN, 1)
-    ms_b, state = [], []
+    ms_b, sh_b, state = [], [], []
     for b in range(8):
         ms, rays = r.time_raycast(5)
         ms_b.append(ms)
+        sh_b.append(r.time_kernel("shadow", 5)[0])
         r.stage(capi.STAGE_TRACE)
         if b < 3:
             state.append([r.path_field(n).copy() for n in ("hit_geom_id", "ray_dir_dist", "hit_uv", "material_id")])
@@ -42,5 +43,5 @@ for cfg in configs:
     else:
         q_ok = all(np.array_equal(a.view(np.uint8), b.view(np.uint8)) for sa, sb in zip(state, base[0]) for a, b in zip(sa[:1] + sa[3:], sb[:1] + sb[3:]))
         same = f"hits_equal={q_ok} radiance_equal={np.array_equal(d.view(np.uint32), base[1].view(np.uint32)) and np.array_equal(i.view(np.uint32), base[2].view(np.uint32))}"
-    print(cfg, "ext ms/bounce:", " ".join(f"{m:.3f}" for m in ms_b), f"sum={sum(ms_b):.3f} frame={fr:.3f} ms", same, flush=True)
+    print(cfg, "ext ms/bounce:", " ".join(f"{m:.3f}" for m in ms_b), f"sum={sum(ms_b):.3f} shadow_sum={sum(sh_b):.3f} frame={fr:.3f} ms", same, flush=True)
     r.free()
