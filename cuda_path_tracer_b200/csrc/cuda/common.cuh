@@ -176,38 +176,61 @@ struct TexturesDev {
 // PathState (src/scene_structs.h:97-117).  Slot == index into this renderer's owned pixels; the
 // GLOBAL pixel index (what seeds the RNG and what the reference calls pixel_idx) is derived from
 // the slot by TileMap, so it is not stored.
-// Storage is three interleaved records per slot, so that the fields a stage reads together share 32-byte sectors (a
-// scattered 16-byte or 4-byte read costs a whole sector of DRAM / L2 traffic either way):
-//   ray [2*slot + 0] = ray_ori        ray [2*slot + 1] = ray_dir_dist      (RayCast reads both, Shade rewrites both)
-//   surf[2*slot + 0] = hit_uv         surf[2*slot + 1] = throughput_pdf    (Logic / Shade read both)
-//   meta[slot] = (hit_geom_id, material_id, remaining_bounces, rng_state)
-// The members below are thin views with operator[], so kernels keep the reference's field names.
+// Storage is three 32-byte records per slot, one per WRITER, so that every store of a stage is a whole 32-byte sector (a
+// partial-sector store costs a fill read plus a whole-sector write-back; the round-1 layout had three of them per ray in
+// RayCast and two per path in Shade -- 2.8x the algorithmic DRAM bytes):
+//   ray  [2*slot] = ray_ori (xyz, 0)            ray  [2*slot+1] = (dir.xyz, FLT_MAX)     written by RayGen / Shade, read by RayCast
+//   hit  [2*slot] = (t, u, v, bits(prim))       hit  [2*slot+1] = (bits(mat), 0, 0, 0)   written by RayCast (t = -1, prim = -1: miss)
+//   state[2*slot] = throughput_pdf              state[2*slot+1] = (bits(remaining_bounces), bits(rng_state), 0, 0)
+//                                                                                        written by RayGen / Shade (Logic: remaining = -1)
+// The reference's fields map onto them as: ray_dir_dist.w after a trace = hit.t; hit_normal = (hit.u, hit.v, 0, 0); hit_geom_id =
+// hit.prim; material_id = hit.mat (ptb_get_path_field assembles these views).  Members with operator[] keep the reference's names.
 struct PoolF4 {                  // every second float4 of an interleaved array
     float4* base;
     __device__ __forceinline__ float4& operator[](int i) const { return base[2 * (size_t)i]; }
 };
 template <typename T>
-struct PoolI {                   // one 32-bit component of the int4 `meta` records
+struct PoolI {                   // one 32-bit word of the 32-byte `state` records
     T* base;
-    __device__ __forceinline__ T& operator[](int i) const { return base[4 * (size_t)i]; }
+    __device__ __forceinline__ T& operator[](int i) const { return base[8 * (size_t)i]; }
 };
-// One 32-byte store for a whole (ray_ori, ray_dir_dist) record (sm_100 STG.256): a full sector, no partial write.
+// One 32-byte store / load of a whole record (sm_100 STG.256 / LDG.256): a full sector, no partial write.
 __device__ __forceinline__ void stg256(float4* p, float4 a, float4 b) {
     asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
                  :: "l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
 }
+__device__ __forceinline__ void ldg256_rw(const float4* p, float4& a, float4& b) {     // data other kernels of the frame rewrite: no .nc
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p) : "memory");
+}
+struct HitRecord { float t, u, v; int prim, mat; };
 struct PathPool {
     PoolF4 ray_ori;
-    PoolF4 ray_dir_dist;
-    PoolF4 hit_uv;               // the reference's `hit_normal`: (u, v, 0, 0) (src/kernels/ray_cast.cu:120)
+    PoolF4 ray_dir_dist;         // .w is FLT_MAX (written with the ray); the hit distance lives in the hit record
     PoolF4 throughput_pdf;
-    PoolI<int> hit_geom_id;
-    PoolI<int> material_id;
     PoolI<int> remaining_bounces;
     PoolI<uint32_t> rng_state;
     float4* ray;                 // [2 * P]
-    float4* surf;                // [2 * P]
-    int4* meta;                  // [P]
+    float4* hit;                 // [2 * P]
+    float4* state;               // [2 * P]
+    __device__ __forceinline__ void store_hit(int slot, float t, float u, float v, int prim, int mat) const {
+        stg256(hit + 2 * (size_t)slot, make_float4(t, u, v, __int_as_float(prim)), make_float4(__int_as_float(mat), 0.0f, 0.0f, 0.0f));
+    }
+    __device__ __forceinline__ HitRecord load_hit(int slot) const {
+        float4 a, b;
+        ldg256_rw(hit + 2 * (size_t)slot, a, b);
+        HitRecord h;
+        h.t = a.x; h.u = a.y; h.v = a.z; h.prim = __float_as_int(a.w); h.mat = __float_as_int(b.x);
+        return h;
+    }
+    __device__ __forceinline__ void store_state(int slot, float4 tp, int remaining, uint32_t rng) const {
+        stg256(state + 2 * (size_t)slot, tp, make_float4(__int_as_float(remaining), __uint_as_float(rng), 0.0f, 0.0f));
+    }
+    __device__ __forceinline__ void load_state(int slot, float4& tp, int& remaining, uint32_t& rng) const {
+        float4 b;
+        ldg256_rw(state + 2 * (size_t)slot, tp, b);
+        remaining = __float_as_int(b.x); rng = __float_as_uint(b.y);
+    }
 };
 
 struct ShadowQueueDev {          // ShadowQueue, src/scene_structs.h:121-131

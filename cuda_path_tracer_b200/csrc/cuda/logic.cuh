@@ -42,11 +42,12 @@ __device__ __forceinline__ int warp_append(bool want, int* counter) {
 
 // One live path after its extension ray: miss -> environment (+ pdf-map MIS) and kill; emissive hit -> emission
 // (+ area-light MIS) and kill; otherwise return the material queue (0..3) the path goes to, -1 if it ended.
-// HAVE_RAY: the caller still holds the material id and (dir.xyz, t) in registers (fused RayCast tail).
+// hit / mat_id / (hit_u, hit_v): the path's hit record.  HAVE_RAY: the caller also holds (dir.xyz, t) in registers (fused
+// RayCast tail); otherwise dd_in.w is t and the direction is read when a branch needs it.
 template <bool HAVE_RAY>
-__device__ __forceinline__ int logic_path(const FrameDev& f, int idx, int hit, int mat_id_in, float4 dd_in) {
-    int remaining = f.pool.remaining_bounces[idx];
-    float4 tp = f.pool.throughput_pdf[idx];
+__device__ __forceinline__ int logic_path(const FrameDev& f, int idx, int hit, int mat_id, float hit_u, float hit_v, float4 dd_in) {
+    float4 tp; int remaining; uint32_t rng_unused;
+    f.pool.load_state(idx, tp, remaining, rng_unused);
     Vec3 throughput(tp.x, tp.y, tp.z);
     float last_pdf = tp.w;
     bool first = (remaining == f.trace_depth);
@@ -79,13 +80,12 @@ __device__ __forceinline__ int logic_path(const FrameDev& f, int idx, int hit, i
         f.pool.remaining_bounces[idx] = -1;
         return -1;
     }
-    int mat_id = HAVE_RAY ? mat_id_in : f.pool.material_id[idx];
     Mat m = load_material(f.materials, mat_id);
     if (m.emittance > 0.0f) {
-        float4 huv = f.pool.hit_uv[idx];
         Vec3 N; float uvx, uvy;
-        surface_properties(f, hit, huv.x, huv.y, m, N, uvx, uvy);
-        float4 dd = HAVE_RAY ? dd_in : f.pool.ray_dir_dist[idx];
+        surface_properties(f, hit, hit_u, hit_v, m, N, uvx, uvy);
+        float4 dd = dd_in;
+        if (!HAVE_RAY) { float4 rd = f.pool.ray_dir_dist[idx]; dd = make_float4(rd.x, rd.y, rd.z, dd_in.w); }
         Vec3 wo = -Vec3(dd.x, dd.y, dd.z);
         float mis = 1.0f;
         if (!first && f.lights.num_lights > 0) {

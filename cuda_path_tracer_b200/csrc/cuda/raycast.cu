@@ -42,17 +42,10 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_exte
             float4 d4 = f.pool.ray_dir_dist[path];
             Hit h = WIDE ? trace_closest_exact(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS)
                          : trace_closest(f.bvh, Vec3(o4.x, o4.y, o4.z), Vec3(d4.x, d4.y, d4.z), my_stack, PTB_RC_THREADS);
-            // write-back, src/kernels/ray_cast.cu:111-121
-            if (h.prim == -1) {
-                f.pool.ray_dir_dist[path].w = -1.0f;
-                f.pool.hit_geom_id[path] = -1;
-            } else {
-                f.pool.ray_dir_dist[path].w = h.t;
-                f.pool.material_id[path] = h.mat;
-                f.pool.hit_geom_id[path] = h.prim;
-                f.pool.hit_uv[path] = make_float4(h.u, h.v, 0.0f, 0.0f);
-            }
-            if (FUSE_LOGIC) queue = logic_path<true>(f, path, h.prim, h.mat, make_float4(d4.x, d4.y, d4.z, h.t));
+            // write-back, src/kernels/ray_cast.cu:111-121: one whole 32-byte hit record (t = -1 on a miss)
+            if (h.prim == -1) h.t = -1.0f;
+            f.pool.store_hit(path, h.t, h.u, h.v, h.prim, h.mat);
+            if (FUSE_LOGIC) queue = logic_path<true>(f, path, h.prim, h.mat, h.u, h.v, make_float4(d4.x, d4.y, d4.z, h.t));
         }
         if (FUSE_LOGIC) logic_dispatch(f, ctr, queue, path);
     }
@@ -125,16 +118,9 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, MINB) k_trace_extension_pl(Fra
         int queue = -1;
         if (fin) {
             Hit h = w.finish(f.bvh, st);
-            if (h.prim == -1) {
-                f.pool.ray_dir_dist[path].w = -1.0f;
-                f.pool.hit_geom_id[path] = -1;
-            } else {
-                f.pool.ray_dir_dist[path].w = h.t;
-                f.pool.material_id[path] = h.mat;
-                f.pool.hit_geom_id[path] = h.prim;
-                f.pool.hit_uv[path] = make_float4(h.u, h.v, 0.0f, 0.0f);
-            }
-            if (FUSE_LOGIC) queue = logic_path<true>(f, path, h.prim, h.mat, make_float4(dir.x, dir.y, dir.z, h.t));
+            if (h.prim == -1) h.t = -1.0f;
+            f.pool.store_hit(path, h.t, h.u, h.v, h.prim, h.mat);
+            if (FUSE_LOGIC) queue = logic_path<true>(f, path, h.prim, h.mat, h.u, h.v, make_float4(dir.x, dir.y, dir.z, h.t));
         }
         if (FUSE_LOGIC) logic_dispatch(f, ctr, queue, path);
         if (fin) path = -1;

@@ -53,11 +53,9 @@ __global__ void __launch_bounds__(kThreads) k_raygen(FrameDev f) {
         + right * f.cam.pixel_length[0] * ((float)x + jx - (float)f.cam.res_x * 0.5f)
         - up * f.cam.pixel_length[1] * ((float)y + jy - (float)f.cam.res_y * 0.5f));
     stg256(f.pool.ray + 2 * (size_t)slot, make_float4(f.cam.pos[0], f.cam.pos[1], f.cam.pos[2], 0.0f), make_float4(dir.x, dir.y, dir.z, FLT_MAX));
-    f.pool.hit_geom_id[slot] = -1;
-    f.pool.material_id[slot] = -1;
-    f.pool.throughput_pdf[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-    f.pool.remaining_bounces[slot] = f.trace_depth;
-    f.pool.rng_state[slot] = seed;
+    // the reference also resets hit_geom_id / material_id to -1 here (src/kernels/ray_gen.cu:68-69); the hit record is only defined
+    // after a trace, and ptb_get_path_field reports -1 until then
+    f.pool.store_state(slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f), f.trace_depth, seed);
     f.q_ext[qpos] = slot;
 }
 
@@ -75,7 +73,8 @@ __global__ void __launch_bounds__(kThreads) k_logic(FrameDev f, int bounce) {
         int idx = -1;
         if (i < count) {
             idx = __ldg(&f.q_ext[i]);
-            queue = logic_path<false>(f, idx, f.pool.hit_geom_id[idx], 0, make_float4(0.0f, 0.0f, 0.0f, 0.0f));
+            const HitRecord h = f.pool.load_hit(idx);
+            queue = logic_path<false>(f, idx, h.prim, h.mat, h.u, h.v, make_float4(0.0f, 0.0f, 0.0f, h.t));
         }
         logic_dispatch(f, ctr, queue, idx);
     }
@@ -93,12 +92,15 @@ struct ShadeOut {
 
 template <int TYPE, bool ENV>
 __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut& out) {
-    float4 dd = f.pool.ray_dir_dist[idx];
-    float4 oo = f.pool.ray_ori[idx];
-    float4 tp = f.pool.throughput_pdf[idx];
-    float4 huv = f.pool.hit_uv[idx];
-    int prim = f.pool.hit_geom_id[idx];
-    int mat_id = f.pool.material_id[idx];
+    float4 oo, dd;                                        // three whole records: ray, hit, state
+    ldg256_rw(f.pool.ray + 2 * (size_t)idx, oo, dd);
+    const HitRecord hr = f.pool.load_hit(idx);
+    float4 tp; int remaining; uint32_t seed;
+    f.pool.load_state(idx, tp, remaining, seed);
+    dd.w = hr.t;                                          // the reference's ray_dir_dist.w after the trace
+    float4 huv = make_float4(hr.u, hr.v, 0.0f, 0.0f);
+    int prim = hr.prim;
+    int mat_id = hr.mat;
     Mat m = load_material(f.materials, mat_id);
     Vec3 N; float uvx, uvy;
     surface_properties(f, prim, huv.x, huv.y, m, N, uvx, uvy);
@@ -120,7 +122,6 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
     Vec3 wo = -dirv;
     Vec3 Ng = make_v3(__ldg(&f.mesh.nor_geom[prim]));
     if (TYPE != MAT_REFRACT) { if (dot3(Ng, wo) < 0.0f) Ng = -Ng; }
-    uint32_t seed = f.pool.rng_state[idx];
     Vec3 throughput(tp.x, tp.y, tp.z);
 
     // ---- next-event estimation (ComputeNextEventEstimation, shading.cu:23-84).  The reference
@@ -204,19 +205,15 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
             alive = false;
         }
         if (alive) {
-            f.pool.throughput_pdf[idx] = make_float4(throughput.x, throughput.y, throughput.z, next_pdf);
+            tp = make_float4(throughput.x, throughput.y, throughput.z, next_pdf);
             stg256(f.pool.ray + 2 * (size_t)idx,
                    make_float4(P.x + bias_n.x * PTB_EPSILON, P.y + bias_n.y * PTB_EPSILON, P.z + bias_n.z * PTB_EPSILON, 0.0f),
                    make_float4(next_dir.x, next_dir.y, next_dir.z, FLT_MAX));
-            f.pool.remaining_bounces[idx] -= 1;
             out.push_ext = true;
-        } else {
-            f.pool.remaining_bounces[idx] = -1;
         }
-    } else {
-        f.pool.remaining_bounces[idx] = -1;
     }
-    f.pool.rng_state[idx] = seed;
+    // one whole state record: a path that ends here keeps its throughput, as in the reference (remaining_bounces = -1, seed stored)
+    f.pool.store_state(idx, tp, out.push_ext ? remaining - 1 : -1, seed);
 }
 
 // One kernel per material queue: a queue's launch carries only its own model's registers and local frame (the

@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(128) k_gbuffer(const __grid_constant__ FrameDe
     if (idx >= f.num_paths) return;
     const Mat4& cur = f.view_proj[0];
     const Mat4& prev = f.view_proj[1];
-    int hit = f.pool.hit_geom_id[idx];
+    const HitRecord hr = f.pool.load_hit(idx);
+    int hit = hr.prim;
     if (hit == -1) {   // sky, src/kernels/logic.cu:66-73
         g.depth[idx] = -1000.0f;
         g.normal_matid[idx] = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
@@ -42,9 +43,9 @@ __global__ void __launch_bounds__(128) k_gbuffer(const __grid_constant__ FrameDe
         return;
     }
     float4 dd = f.pool.ray_dir_dist[idx];
-    float t = dd.w;
-    float4 huv = f.pool.hit_uv[idx];
-    int mat_id = f.pool.material_id[idx];
+    float t = hr.t;
+    float4 huv = make_float4(hr.u, hr.v, 0.0f, 0.0f);
+    int mat_id = hr.mat;
     Mat m = load_material(f.materials, mat_id);
     Vec3 N; float uvx, uvy;
     surface_properties(f, hit, huv.x, huv.y, m, N, uvx, uvy);

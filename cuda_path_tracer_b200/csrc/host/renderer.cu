@@ -56,6 +56,8 @@ struct ptb_renderer {
     // staged execution state
     int stage_bounce = 0;                    // bounce the next TRACE / LOGIC / SHADE works on
     int logic_bounce = 0;                    // bounce of the last LOGIC (material queue counters)
+    bool stage_traced = false;               // staged frame: TRACE of stage_bounce has run, its SHADE has not
+    bool hit_valid = false;                  // the hit records belong to the current frame (false between RAYGEN and the first trace)
 
     // scratch for batched tracing / timing
     void* scratch = nullptr;
@@ -448,16 +450,13 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     f.trace_depth = cfg.trace_depth > 0 ? cfg.trace_depth : scene->trace_depth;
     if (f.trace_depth < 1) f.trace_depth = 1;
     TRY(dev_alloc(r, f.pool.ray, 2 * P));
-    TRY(dev_alloc(r, f.pool.surf, 2 * P));
-    TRY(dev_alloc(r, f.pool.meta, P));
+    TRY(dev_alloc(r, f.pool.hit, 2 * P));
+    TRY(dev_alloc(r, f.pool.state, 2 * P));
     f.pool.ray_ori.base = f.pool.ray;
     f.pool.ray_dir_dist.base = f.pool.ray + 1;
-    f.pool.hit_uv.base = f.pool.surf;
-    f.pool.throughput_pdf.base = f.pool.surf + 1;
-    f.pool.hit_geom_id.base = reinterpret_cast<int*>(f.pool.meta) + 0;
-    f.pool.material_id.base = reinterpret_cast<int*>(f.pool.meta) + 1;
-    f.pool.remaining_bounces.base = reinterpret_cast<int*>(f.pool.meta) + 2;
-    f.pool.rng_state.base = reinterpret_cast<uint32_t*>(f.pool.meta) + 3;
+    f.pool.throughput_pdf.base = f.pool.state;
+    f.pool.remaining_bounces.base = reinterpret_cast<int*>(f.pool.state + 1) + 0;
+    f.pool.rng_state.base = reinterpret_cast<uint32_t*>(f.pool.state + 1) + 1;
     TRY(dev_alloc(r, f.shadow.ray_ori_tmax, nee_factor * P));
     TRY(dev_alloc(r, f.shadow.ray_dir, nee_factor * P));
     TRY(dev_alloc(r, f.shadow.radiance, nee_factor * P));
@@ -478,9 +477,9 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     TRYCU(cudaMemsetAsync(f.direct, 0, nee_factor * 3 * P * sizeof(float), r->stream));
     TRYCU(cudaMemsetAsync(f.indirect, 0, 3 * P * sizeof(float), r->stream));
     // InitPathPoolKernel (src/pathtrace_wavefront.cu:183-190): every slot starts dead
-    TRYCU(cudaMemsetAsync(f.pool.meta, 0xff, P * sizeof(int4), r->stream));   // remaining_bounces = hit_geom_id = -1
+    TRYCU(cudaMemsetAsync(f.pool.state, 0xff, 2 * P * sizeof(float4), r->stream));   // remaining_bounces = -1
+    TRYCU(cudaMemsetAsync(f.pool.hit, 0xff, 2 * P * sizeof(float4), r->stream));     // hit_geom_id = material_id = -1
     TRYCU(cudaMemsetAsync(f.pool.ray, 0, 2 * P * sizeof(float4), r->stream));
-    TRYCU(cudaMemsetAsync(f.pool.surf, 0, 2 * P * sizeof(float4), r->stream));
 
     // ---- first-bounce G-buffer (initSVGF buffers, src/wavefront_internal.cu:286-300), on request
     f.view_proj = nullptr;
@@ -593,6 +592,8 @@ int ptb_render_many(ptb_renderer* r, int32_t first, int32_t count) {
         }
         r->device_iteration = it + 1;
         r->frames++;
+        r->stage_traced = false;
+        r->hit_valid = true;
     }
     CU(cudaGetLastError());
     return PTB_OK;
@@ -885,11 +886,15 @@ int ptb_stage_run(ptb_renderer* r, int32_t stage, int32_t iteration) {
             r->device_iteration = iteration;   // frame_end is not run in staged mode
             r->stage_bounce = 0;
             r->logic_bounce = 0;
+            r->stage_traced = false;
+            r->hit_valid = false;
             break;
         case PTB_STAGE_TRACE:
             if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
             r->kernel_launches += launch_trace(f, r->stage_bounce, r->launch, r->stream);
             if (f.env.nee) r->kernel_launches += launch_fold_env(f, r->stream);
+            r->stage_traced = true;
+            r->hit_valid = true;
             break;
         case PTB_STAGE_LOGIC:
             if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
@@ -900,6 +905,7 @@ int ptb_stage_run(ptb_renderer* r, int32_t stage, int32_t iteration) {
             if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
             r->kernel_launches += launch_shade(f, r->stage_bounce, r->launch, r->stream);
             r->stage_bounce++;
+            r->stage_traced = false;
             break;
         default:
             return fail(PTB_ERR_INVALID, "ptb_stage_run: unknown stage");
@@ -968,30 +974,53 @@ int ptb_get_shadow_queue(ptb_renderer* r, float* ori_tmax4, float* dir4, float* 
 int ptb_get_path_field(ptb_renderer* r, int32_t field, void* dst, size_t bytes) {
     if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_path_field: null argument");
     CU(cudaSetDevice(r->device));
+    // The reference's PathState fields as VIEWS of the three 32-byte records of a slot (common.cuh): src / pitch select a word
+    // range of a record; ray_dir_dist.w and hit_normal are assembled below.
     const char* src;
-    size_t elem, pitch;           // element size and the stride between consecutive slots (interleaved records, common.cuh)
+    size_t elem, pitch = 32;
     const PathPool& pool = r->frame.pool;
     switch (field) {
-        case PTB_PF_RAY_ORI: src = (const char*)pool.ray; elem = 16; pitch = 32; break;
-        case PTB_PF_RAY_DIR_DIST: src = (const char*)(pool.ray + 1); elem = 16; pitch = 32; break;
-        case PTB_PF_HIT_UV: src = (const char*)pool.surf; elem = 16; pitch = 32; break;
-        case PTB_PF_THROUGHPUT_PDF: src = (const char*)(pool.surf + 1); elem = 16; pitch = 32; break;
-        case PTB_PF_HIT_GEOM_ID: src = (const char*)pool.meta + 0; elem = 4; pitch = 16; break;
-        case PTB_PF_MATERIAL_ID: src = (const char*)pool.meta + 4; elem = 4; pitch = 16; break;
-        case PTB_PF_REMAINING_BOUNCES: src = (const char*)pool.meta + 8; elem = 4; pitch = 16; break;
-        case PTB_PF_RNG_STATE: src = (const char*)pool.meta + 12; elem = 4; pitch = 16; break;
+        case PTB_PF_RAY_ORI: src = (const char*)pool.ray; elem = 16; break;
+        case PTB_PF_RAY_DIR_DIST: src = (const char*)(pool.ray + 1); elem = 16; break;
+        case PTB_PF_HIT_UV: src = (const char*)pool.hit; elem = 16; break;                 // (t, u, v, prim) -> (u, v, 0, 0) below
+        case PTB_PF_THROUGHPUT_PDF: src = (const char*)pool.state; elem = 16; break;
+        case PTB_PF_HIT_GEOM_ID: src = (const char*)pool.hit + 12; elem = 4; break;
+        case PTB_PF_MATERIAL_ID: src = (const char*)pool.hit + 16; elem = 4; break;
+        case PTB_PF_REMAINING_BOUNCES: src = (const char*)pool.state + 16; elem = 4; break;
+        case PTB_PF_RNG_STATE: src = (const char*)pool.state + 20; elem = 4; break;
         default: return fail(PTB_ERR_INVALID, "ptb_get_path_field: unknown field");
     }
     const TileMap& tm = r->frame.tile;
     const size_t full = (size_t)tm.width * tm.height * elem;
     if (bytes < full) return fail(PTB_ERR_INVALID, "ptb_get_path_field: buffer smaller than width*height elements");
     CU(cudaStreamSynchronize(r->stream));
+    const size_t n = (size_t)tm.owned_pixels;
+    std::vector<char> tmp(n * elem);
+    CU(cudaMemcpy2D(tmp.data(), elem, src, pitch, elem, n, cudaMemcpyDeviceToHost));
+    if (field == PTB_PF_HIT_UV) {
+        float* p = reinterpret_cast<float*>(tmp.data());
+        for (size_t i = 0; i < n; i++) { p[4 * i] = p[4 * i + 1]; p[4 * i + 1] = p[4 * i + 2]; p[4 * i + 2] = 0.0f; p[4 * i + 3] = 0.0f; }
+    } else if ((field == PTB_PF_HIT_GEOM_ID || field == PTB_PF_MATERIAL_ID) && !r->hit_valid) {
+        // RayGen resets both to -1 in the reference (src/kernels/ray_gen.cu:68-69); here the hit record is undefined until the
+        // frame's first trace
+        int32_t* p = reinterpret_cast<int32_t*>(tmp.data());
+        for (size_t i = 0; i < n; i++) p[i] = -1;
+    } else if (field == PTB_PF_RAY_DIR_DIST && r->stage_traced) {
+        // between TRACE and SHADE of a staged frame the reference holds the hit distance (or -1) in ray_dir_dist.w of every path
+        // of the bounce's extension queue (src/kernels/ray_cast.cu:111-121)
+        int count = 0;
+        CU(cudaMemcpy(&count, r->frame.ctr + r->stage_bounce * CTR_STRIDE + CTR_EXT, sizeof(int), cudaMemcpyDeviceToHost));
+        std::vector<int32_t> q((size_t)(count > 0 ? count : 0));
+        std::vector<float> t(n);
+        if (count > 0) CU(cudaMemcpy(q.data(), r->frame.q_ext, (size_t)count * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        CU(cudaMemcpy2D(t.data(), 4, pool.hit, 32, 4, n, cudaMemcpyDeviceToHost));
+        float* p = reinterpret_cast<float*>(tmp.data());
+        for (int32_t slot : q) p[4 * (size_t)slot + 3] = t[slot];
+    }
     if (tm.world <= 1) {
-        CU(cudaMemcpy2D(dst, elem, src, pitch, elem, (size_t)tm.owned_pixels, cudaMemcpyDeviceToHost));
+        memcpy(dst, tmp.data(), n * elem);
         return PTB_OK;
     }
-    std::vector<char> tmp((size_t)tm.owned_pixels * elem);
-    CU(cudaMemcpy2D(tmp.data(), elem, src, pitch, elem, (size_t)tm.owned_pixels, cudaMemcpyDeviceToHost));
     for (int i = 0; i < tm.owned_pixels; i++)
         memcpy((char*)dst + (size_t)tm.global_pixel(i) * elem, tmp.data() + (size_t)i * elem, elem);
     return PTB_OK;
