@@ -91,6 +91,7 @@ SIGNATURES = {
     "ptb_scene_from_arrays": (C.c_int, [P, P, P, P, C.c_int32, P, P, C.c_int32, P, C.c_int32, C.POINTER(Camera), C.c_int32, C.POINTER(P)]),
     "ptb_scene_set_environment": (C.c_int, [P, P, C.c_int32, C.c_int32]),
     "ptb_scene_add_texture": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "ptb_scene_get_texture": (C.c_int64, [P, C.c_int32, P, C.c_size_t, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "ptb_scene_set_environment_table": (C.c_int, [P, C.c_int32, C.c_int32, P, P, C.c_int32, C.c_int32]),
     "ptb_scene_set_camera": (C.c_int, [P, C.POINTER(C.c_int32 * 2), C.c_float, C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.POINTER(C.c_float * 3), C.c_int32]),
     "ptb_scene_save_cache": (C.c_int, [P, C.c_char_p]),

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cctype>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -106,16 +107,31 @@ static bool decode_tga(const std::vector<uint8_t>& d, int& w, int& h, int& ch, s
     return true;
 }
 
+// png_decode.cpp
+bool decode_png(const std::vector<uint8_t>& d, int& w, int& h, int& ch, std::vector<uint8_t>& px, std::string& err);
+bool decode_tga_rle(const std::vector<uint8_t>& d, int& w, int& h, int& ch, std::vector<uint8_t>& px, std::string& err);
+
+// What stbi_load reads and this loader reads too: PNG (8-bit and below, non-interlaced), BMP 24/32, TGA true-colour / grey
+// (plain and run-length), PNM P5/P6.  `err` starts with "cannot read" when the file itself is missing (the reference then
+// prints a message and renders untextured, src/scene.cpp:141-146) and with "unsupported" when the file is there but in a
+// format or variant this loader does not decode (JPEG, GIF, PSD, 16-bit / interlaced PNG, colour-mapped TGA): the scene
+// loader turns that into PTB_ERR_UNSUPPORTED instead of silently rendering something else than the reference would.
 bool load_image_u8(const std::string& path, int& w, int& h, int& channels, std::vector<uint8_t>& px, std::string& err) {
     std::vector<uint8_t> d;
     if (!read_file(path, d) || d.size() < 4) { err = "cannot read " + path; return false; }
-    if (d[0] == 'P' && (d[1] == '5' || d[1] == '6')) return decode_pnm(d, w, h, channels, px, err);
-    if (d[0] == 'B' && d[1] == 'M') return decode_bmp(d, w, h, channels, px, err);
-    size_t dot = path.find_last_of('.');
-    std::string ext = dot == std::string::npos ? "" : path.substr(dot);
-    if (ext == ".tga" || ext == ".TGA") return decode_tga(d, w, h, channels, px, err);
-    err = "unsupported image format (PNM/BMP/TGA only): " + path;
-    return false;
+    bool ok;
+    if (d.size() >= 8 && d[0] == 0x89 && d[1] == 'P' && d[2] == 'N' && d[3] == 'G') ok = decode_png(d, w, h, channels, px, err);
+    else if (d[0] == 'P' && (d[1] == '5' || d[1] == '6')) ok = decode_pnm(d, w, h, channels, px, err);
+    else if (d[0] == 'B' && d[1] == 'M') ok = decode_bmp(d, w, h, channels, px, err);
+    else {
+        size_t dot = path.find_last_of('.');
+        std::string ext = dot == std::string::npos ? "" : path.substr(dot);
+        for (char& c : ext) c = (char)tolower((unsigned char)c);
+        if (ext == ".tga") ok = (d.size() >= 3 && (d[2] == 10 || d[2] == 11)) ? decode_tga_rle(d, w, h, channels, px, err) : decode_tga(d, w, h, channels, px, err);
+        else { err = "unsupported: image format of " + path + " (PNG, BMP, TGA and PNM are decoded; JPEG, GIF, PSD are not)"; return false; }
+    }
+    if (!ok && err.compare(0, 11, "unsupported") != 0) err = "unsupported: " + err + " (" + path + ")";
+    return ok;
 }
 
 static void rgbe_to_float(const uint8_t* in, float* out) {

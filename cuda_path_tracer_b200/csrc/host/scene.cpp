@@ -154,7 +154,9 @@ static int load_texture(ptb_scene& s, const std::string& path) {   // src/scene.
     std::vector<uint8_t> px;
     std::string err;
     if (!load_image_u8(path, w, h, ch, px, err)) {
-        fprintf(stderr, "ptb200: could not load texture %s (%s)\n", path.c_str(), err.c_str());
+        // a file that is there but that this loader cannot decode must not become a silently untextured render
+        if (err.compare(0, 11, "unsupported") == 0) throw std::runtime_error("texture " + err);
+        fprintf(stderr, "ptb200: could not load texture %s (%s)\n", path.c_str(), err.c_str());   // missing file: as the reference, id -1
         return -1;
     }
     HostTexture t;

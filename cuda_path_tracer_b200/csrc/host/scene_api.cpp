@@ -37,7 +37,7 @@ int ptb_scene_load(const char* json_path, ptb_scene** out) {
     } catch (const std::exception& e) {
         delete s;
         std::string msg = e.what();
-        int code = msg.find("open") != std::string::npos ? PTB_ERR_IO : PTB_ERR_PARSE;
+        int code = msg.find("unsupported") != std::string::npos ? PTB_ERR_UNSUPPORTED : msg.find("open") != std::string::npos ? PTB_ERR_IO : PTB_ERR_PARSE;
         return fail(code, "ptb_scene_load: " + msg);
     }
     *out = s;
@@ -105,6 +105,19 @@ int ptb_scene_add_texture(ptb_scene* s, const void* pixels, int32_t width, int32
     }
     s->textures.push_back(std::move(t));
     return (int)s->textures.size() - 1;
+}
+
+int64_t ptb_scene_get_texture(const ptb_scene* s, int32_t id, void* dst, size_t bytes, int32_t* width, int32_t* height, int32_t* format) {
+    if (!s) return fail(PTB_ERR_INVALID, "ptb_scene_get_texture: null scene");
+    if (id < 0 || id >= (int32_t)s->textures.size()) return fail(PTB_ERR_INVALID, "ptb_scene_get_texture: texture id out of range");
+    const HostTexture& t = s->textures[id];
+    if (width) *width = t.width;
+    if (height) *height = t.height;
+    if (format) *format = !t.is_float ? PTB_TEX_RGBA8 : t.channels == 1 ? PTB_TEX_R32F : PTB_TEX_RGBA32F;
+    const void* src = t.is_float ? (const void*)t.f32.data() : (const void*)t.rgba8.data();
+    const size_t size = t.is_float ? t.f32.size() * sizeof(float) : t.rgba8.size();
+    if (dst && bytes) memcpy(dst, src, bytes < size ? bytes : size);
+    return (int64_t)size;
 }
 
 int ptb_scene_set_environment_table(ptb_scene* s, int32_t env_tex_id, int32_t pdf_map_id, const float* probs, const int32_t* aliases,

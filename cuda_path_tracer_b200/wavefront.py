@@ -102,6 +102,17 @@ class Scene:
     def array(self, name):
         return _fetch(lib.ptb_scene_get_array, self._h, SA[name])
 
+    def texture(self, tex_id):
+        """Decoded texture `tex_id` as it is uploaded: uint8 (h, w, 4), or float32 (h, w) / (h, w, 4) for the environment maps."""
+        w, h, fmt = C.c_int32(), C.c_int32(), C.c_int32()
+        size = check(lib.ptb_scene_get_texture(self._h, tex_id, None, 0, C.byref(w), C.byref(h), C.byref(fmt)))
+        out = np.empty(size, np.uint8)
+        check(lib.ptb_scene_get_texture(self._h, tex_id, ptr(out), size, None, None, None))
+        if fmt.value == 0:
+            return out.reshape(h.value, w.value, 4)
+        f = out.view(np.float32)
+        return f.reshape(h.value, w.value) if fmt.value == 1 else f.reshape(h.value, w.value, 4)
+
     def free(self):
         if self._h:
             lib.ptb_scene_free(self._h)

@@ -101,6 +101,12 @@ enum { PTB_TEX_RGBA8 = 0, PTB_TEX_R32F = 1, PTB_TEX_RGBA32F = 2 };
 int ptb_scene_add_texture(ptb_scene* s, const void* pixels, int32_t width, int32_t height, int32_t format, int32_t clamp_y);
 int ptb_scene_set_environment_table(ptb_scene* s, int32_t env_tex_id, int32_t pdf_map_id, const float* probs,
                                     const int32_t* aliases, int32_t width, int32_t height);
+/* The decoded image behind texture `id` as it will be uploaded (what Scene::loadTexture hands to createTexture, src/scene.cpp:148-172:
+ * uchar4 with grey replicated and alpha 255 where the file has none): copies min(bytes, size), returns the full size in bytes or
+ * a negative status; width / height / format (PTB_TEX_*) may be NULL.  Texture files are decoded by this library's own PNG / BMP /
+ * TGA / PNM readers (the reference uses stb_image); a file that exists but cannot be decoded makes ptb_scene_load fail with
+ * PTB_ERR_UNSUPPORTED, a missing file leaves the material untextured as in the reference (src/scene.cpp:141-146). */
+int64_t ptb_scene_get_texture(const ptb_scene* s, int32_t id, void* dst, size_t bytes, int32_t* width, int32_t* height, int32_t* format);
 /* Recompute camera.view/right/up/fov/pixel_length from eye/lookat/up/fovy/resolution
  * (src/scene.cpp:560-572) and store it in the scene. */
 int ptb_scene_set_camera(ptb_scene* s, const int32_t resolution[2], float fovy_deg,

@@ -244,7 +244,25 @@ static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// --stbi FILE...: the reference's own image decoder (stb_image 2.06, external/include/stb_image.h, compiled by src/stb_image.cpp)
+// exactly as Scene::loadTexture calls it (src/scene.cpp:139): size, channel count and a position-weighted sum of the pixel bytes
+extern "C" unsigned char* stbi_load(char const* filename, int* x, int* y, int* comp, int req_comp);
+extern "C" const char* stbi_failure_reason(void);
+static int stbi_report(int argc, char** argv) {
+    for (int i = 2; i < argc; i++) {
+        int w = 0, h = 0, c = 0;
+        unsigned char* px = stbi_load(argv[i], &w, &h, &c, 0);
+        if (!px) { printf("REFSTBI {\"file\": \"%s\", \"ok\": false, \"reason\": \"%s\"}\n", argv[i], stbi_failure_reason() ? stbi_failure_reason() : ""); continue; }
+        unsigned long long s = 0;
+        const size_t n = (size_t)w * h * c;
+        for (size_t k = 0; k < n; k++) s += ((unsigned long long)px[k] + 1ull) * ((unsigned long long)k * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull);
+        printf("REFSTBI {\"file\": \"%s\", \"ok\": true, \"w\": %d, \"h\": %d, \"channels\": %d, \"sum\": \"%016llx\"}\n", argv[i], w, h, c, s);
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc >= 3 && std::string(argv[1]) == "--stbi") return stbi_report(argc, argv);
     if (argc < 3) {
         fprintf(stderr,
             "usage: refdump SCENE.json OUTDIR [--iters N] [--stages] [--selfcheck] [--bench K W] [--mega] [--no-dump] [--views] [--denoise] [--denoise-bench K]\n");
