@@ -234,7 +234,7 @@ static void run_extension(const FrameDev& f, int bounce, int* cursor, const Laun
 #define PTB_PL_B(W, S) do { if (c.rc_minb == 8) PTB_PL_T(W, S, 8); if (c.rc_minb == 9) PTB_PL_T(W, S, 9); PTB_PL_T(W, S, 10); } while (0)
     if (c.rc_mode == 1) { if (c.rc_stack) PTB_PL_B(WalkBinary, StackHybrid<8>); else PTB_PL_B(WalkBinary, StackShared); }
     if (c.rc_mode == 2) { if (c.rc_stack) PTB_PL_B(WalkBq, StackHybrid<8>); else PTB_PL_B(WalkBq, StackShared); }
-    if (c.rc_mode == 3) PTB_PL_B(WalkWide, StackShared);
+    if (c.rc_mode == 3) PTB_PL_B(WalkWide, StackShared);      // (hybrid stacks of 8 / 16 shared entries: 10.52-10.61 ms against 10.19)
 #undef PTB_PL_B
 #undef PTB_PL_T
 #undef PTB_PL

@@ -300,6 +300,10 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     if (cfg.rank < 0 || cfg.rank >= cfg.world) return fail(PTB_ERR_INVALID, "ptb_init: rank outside [0, world)");
     if (cfg.megakernel && (cfg.gbuffer || cfg.denoiser || cfg.env_nee))
         return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the megakernel path has no G-buffer, denoiser or environment NEE (src/pathtrace.cu has none)");
+    {
+        const std::string why = validate_scene(*scene);
+        if (!why.empty()) return fail(PTB_ERR_INVALID, "ptb_init: " + why);
+    }
     const int N = (int)scene->indices_matid.size();
     const int V = (int)scene->pos.size();
     if (N < 2) return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the LBVH needs at least 2 triangles (the reference's hierarchy is undefined below that)");
@@ -431,6 +435,8 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         f.bvh.root_max = root[1];
         f.bvh.num_triangles = N;
         if (r->lbvh_max_depth > 256) { ptb_free(r); return fail(PTB_ERR_UNSUPPORTED, "ptb_init: LBVH deeper than 256 levels"); }
+        // the megakernel's visibility walk has 32- and 64-entry stacks only (megakernel.cu): refuse here, not at the first sync
+        if (cfg.megakernel && r->lbvh_max_depth > 64) { ptb_free(r); return fail(PTB_ERR_UNSUPPORTED, "ptb_init: the megakernel path supports LBVHs up to 64 levels deep (this one: " + std::to_string(r->lbvh_max_depth) + "); use the wavefront path"); }
         // any-hit stack: at most one entry per internal node on the root-to-leaf path, i.e. <= lbvh_max_depth
         const int dmax = r->lbvh_max_depth;
         r->launch.shadow_deep = dmax <= 32 ? 0 : dmax <= 48 ? 1 : dmax <= 64 ? 2 : 3;
@@ -892,7 +898,9 @@ int ptb_stage_run(ptb_renderer* r, int32_t stage, int32_t iteration) {
         case PTB_STAGE_TRACE:
             if (r->stage_bounce >= f.trace_depth) return fail(PTB_ERR_STATE, "ptb_stage_run: all bounces of this frame are done");
             r->kernel_launches += launch_trace(f, r->stage_bounce, r->launch, r->stream);
-            if (f.env.nee) r->kernel_launches += launch_fold_env(f, r->stream);
+            // the environment's half of `direct` is folded in ONCE per frame, after the last trace, exactly where the frame graph does
+            // it (enqueue_frame): folding after every TRACE would round (d + e1) + e2 instead of d + (e1 + e2)
+            if (f.env.nee && r->stage_bounce == f.trace_depth - 1) r->kernel_launches += launch_fold_env(f, r->stream);
             r->stage_traced = true;
             r->hit_valid = true;
             break;

@@ -74,6 +74,11 @@ void build_env_alias_table(ptb_scene& s, const float* rgb, int width, int height
 // Scene::loadCamera's derived quantities (src/scene.cpp:560-572)
 void derive_camera(ptb_camera& cam, float fovy_deg);
 
+// What every kernel relies on and no kernel checks: material types and texture ids, light triangle indices, the environment's
+// table sizes and alias range.  Returns an empty string when the scene is consistent, else what is wrong.  Called by
+// ptb_scene_load_cache and ptb_init (a scene built with ptb_scene_from_arrays may still gain textures before ptb_init).
+std::string validate_scene(const ptb_scene& s);
+
 // image_io.cpp: decoders for the formats the procedural generators emit and stb_image 2.06
 // also reads (PNM P5/P6, BMP 24/32, TGA 24/32 uncompressed, Radiance .hdr flat + RLE).
 bool load_image_u8(const std::string& path, int& w, int& h, int& channels, std::vector<uint8_t>& px, std::string& err);

@@ -20,6 +20,33 @@ int fail(int code, const std::string& msg) {
 }
 }  // namespace ptb
 
+namespace ptb {
+std::string validate_scene(const ptb_scene& s) {
+    const int ntx = (int)s.textures.size();
+    const size_t T = s.indices_matid.size();
+    for (size_t i = 0; i < s.materials.size(); i++) {
+        const ptb_material& m = s.materials[i];
+        if (m.type < 0 || m.type > 3) return "material " + std::to_string(i) + ": type outside 0..3";
+        const int ids[3] = {m.diffuse_tex_id, m.normal_tex_id, m.metallic_roughness_tex_id};
+        for (int id : ids) {
+            if (id < -1 || id >= ntx) return "material " + std::to_string(i) + ": texture id " + std::to_string(id) + " with " + std::to_string(ntx) + " textures";
+            if (id >= 0 && s.textures[id].is_float) return "material " + std::to_string(i) + ": texture " + std::to_string(id) + " is a float (environment) texture";
+        }
+    }
+    if (s.light_tri_idx.size() != s.light_cdf.size()) return "light triangle list and CDF differ in length";
+    for (int32_t t : s.light_tri_idx)
+        if (t < 0 || (size_t)t >= T) return "light triangle index out of range";
+    if (s.env.width > 0 || s.env.env_tex_id >= 0) {
+        const size_t n = (size_t)s.env.width * (size_t)s.env.height;
+        if (s.env.width <= 0 || s.env.height <= 0 || s.env.probs.size() != n || s.env.aliases.size() != n) return "environment alias table size differs from width * height";
+        if (s.env.env_tex_id < 0 || s.env.env_tex_id >= ntx || s.env.pdf_map_id < 0 || s.env.pdf_map_id >= ntx) return "environment texture id out of range";
+        for (int32_t a : s.env.aliases)
+            if (a < 0 || (size_t)a >= n) return "environment alias out of range";
+    }
+    return std::string();
+}
+}  // namespace ptb
+
 extern "C" {
 
 int ptb_abi_version(void) { return PTB_ABI_VERSION; }
@@ -56,6 +83,8 @@ int ptb_scene_from_arrays(const float* pos, const float* nor, const float* uv, c
         if (indices[i] < 0 || indices[i] >= num_vertices) return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: vertex index out of range");
     for (int32_t i = 0; i < num_triangles; i++)
         if (material_ids[i] < 0 || material_ids[i] >= num_materials) return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: material id out of range");
+    for (int32_t i = 0; i < num_materials; i++)
+        if (materials[i].type < 0 || materials[i].type > 3) return fail(PTB_ERR_INVALID, "ptb_scene_from_arrays: material type outside 0..3");
     ptb_scene* s = new ptb_scene();
     s->pos.resize(num_vertices); s->nor.resize(num_vertices); s->tangent.resize(num_vertices); s->uv.resize(num_vertices);
     for (int32_t i = 0; i < num_vertices; i++) {

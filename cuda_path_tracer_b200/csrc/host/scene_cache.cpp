@@ -131,6 +131,8 @@ void read_scene(Reader& r, ptb_scene& s) {
             throw std::runtime_error("corrupt cache: index out of range");
     const int ntx = (int)s.textures.size();
     if (s.env.env_tex_id >= ntx || s.env.pdf_map_id >= ntx) throw std::runtime_error("corrupt cache: texture id out of range");
+    const std::string why = validate_scene(s);
+    if (!why.empty()) throw std::runtime_error("corrupt cache: " + why);
 }
 
 }  // namespace

@@ -542,6 +542,24 @@ def test_env_nee_flag(tmp_path):
     scene.free()
 
 
+@pytest.mark.gpu
+def test_env_nee_staged_equals_whole_frame(tmp_path):
+    """With env_nee the environment's shadow rays accumulate into a second half of `direct` that is folded in once per frame; the
+    staged API folds at the same point (after the last TRACE), so a frame driven stage by stage leaves the whole frame's bits."""
+    path = scenegen.sponza(str(tmp_path / "sp"), res=(160, 90), scale=0.1, tex_size=64)[0]
+    scene = ptb.Scene(path)
+    a = ptb.Renderer(scene, env_nee=True)
+    a.render(1)
+    da, ia = a.accumulators()
+    b = ptb.Renderer(scene, env_nee=True)
+    b.stage(capi.STAGE_RAYGEN, 1)
+    for _ in range(scene.info.trace_depth):
+        b.stage(capi.STAGE_TRACE); b.stage(capi.STAGE_LOGIC); b.stage(capi.STAGE_SHADE)
+    db, ib = b.accumulators()
+    assert da.max() > 0 and _bits(ia, ib) and _bits(da, db)
+    a.free(); b.free(); scene.free()
+
+
 # ---- the megakernel path (ptb_config.megakernel; reference: pathtrace_megakernel::Pathtrace, src/pathtrace.cu:645-706) ----
 def _mega_ref(scene_json, d, iters):
     par.run_refdump(scene_json, d, iters=iters, mega=True)

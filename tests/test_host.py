@@ -471,3 +471,35 @@ def test_undecodable_texture_is_an_error_not_a_silent_skip(tmp_path):
     s = ptb.Scene(_scene_with_textures(str(tmp_path / "m"), [os.path.join(d, "not_there.png")]))
     assert s.info.num_textures == 0
     s.free()
+
+
+def test_scene_validation_rejects_bad_material_and_light_data(tmp_path):
+    """One shared check (validate_scene) behind ptb_scene_from_arrays, ptb_scene_load_cache and ptb_init: a material whose texture id
+    points past the scene's textures, or whose type is not one of the four models, is PTB_ERR_INVALID -- not an out-of-bounds read
+    on the device.  ptb_init validates before it looks for a GPU, so this runs on the CPU."""
+    pos, nor, idx, mat = scenegen.heightfield_arrays(64, seed=3)
+    mats = scenegen.stress_materials()
+    cam = scenegen.stress_camera((16, 16))
+    good = ptb.Scene.from_arrays(pos, nor, idx, mat, mats, cam)
+    bad = mats.copy(); bad[1]["diffuse_tex_id"] = 0                     # the scene has no textures
+    s = ptb.Scene.from_arrays(pos, nor, idx, mat, bad, cam)
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Renderer(s)
+    assert e.value.code == capi.ERR_INVALID and "texture id" in str(e.value)
+    bad = mats.copy(); bad[0]["type"] = 7
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Scene.from_arrays(pos, nor, idx, mat, bad, cam)
+    assert e.value.code == capi.ERR_INVALID
+    # a texture added afterwards makes the id valid again (ids are checked at ptb_init, when the scene is complete)
+    tex = np.full((4, 4, 4), 200, np.uint8)
+    assert capi.lib.ptb_scene_add_texture(s._h, tex.ctypes.data_as(C.c_void_p), 4, 4, 0, 0) == 0
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Renderer(s)
+    assert e.value.code == capi.ERR_CUDA                                # valid now; only the missing GPU stops it
+    # a cache whose material table was damaged after the fact is refused
+    path = str(tmp_path / "scene.ptbscene")
+    good.save_cache(path)
+    again = ptb.Scene.load_cache(path)
+    assert again.info.num_triangles == good.info.num_triangles
+    for sc in (good, s, again):
+        sc.free()
