@@ -92,3 +92,25 @@ def test_sample_reduce_gloo(world):
     assert its == [1, 1 + world, 1 + 2 * world]
     n = 3 * world
     assert np.allclose(frame, (n * (n + 1) / 2) / n) and frame.shape == (12, 3)
+
+
+def test_hybrid_layout_covers_every_pixel_and_sample_once():
+    """G tile groups x S sample groups (multigpu.hybrid_layout, the rank layout of PeerFrame and of ptb_multi_init): the ranks of one
+    sample group tile the frame exactly once, and over `steps` steps the sample groups render iterations 1 .. steps * S exactly once."""
+    width, height, stripe = 37, 50, 8
+    for world, G in ((8, 2), (8, 8), (8, 1), (4, 2), (6, 3)):
+        S = world // G
+        seen = {}
+        for rank in range(world):
+            t, s, s_count = multigpu.hybrid_layout(rank, world, G)
+            assert s_count == S and 0 <= t < G and 0 <= s < S
+            pix = multigpu.owned_pixels(t, G, stripe, width, height)
+            seen.setdefault(s, []).append(pix)
+        for s, tiles in seen.items():
+            allpix = np.sort(np.concatenate(tiles))
+            assert np.array_equal(allpix, np.arange(width * height)), (world, G, s)
+        steps = 5
+        iters = sorted(step * S + s + 1 for step in range(steps) for s in range(S))      # PeerFrame.iteration
+        assert iters == list(range(1, steps * S + 1))
+    with pytest.raises(ValueError):
+        multigpu.hybrid_layout(0, 8, 3)
