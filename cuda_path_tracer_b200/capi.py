@@ -88,6 +88,7 @@ SIGNATURES = {
     "ptb_last_error": (C.c_char_p, []),
     "ptb_device_count": (C.c_int, []),
     "ptb_scene_load": (C.c_int, [C.c_char_p, C.POINTER(P)]),
+    "ptb_scene_load_device": (C.c_int, [C.c_char_p, C.c_int32, C.POINTER(P)]),
     "ptb_scene_from_arrays": (C.c_int, [P, P, P, P, C.c_int32, P, P, C.c_int32, P, C.c_int32, C.POINTER(Camera), C.c_int32, C.POINTER(P)]),
     "ptb_scene_set_environment": (C.c_int, [P, P, C.c_int32, C.c_int32]),
     "ptb_scene_add_texture": (C.c_int, [P, P, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),

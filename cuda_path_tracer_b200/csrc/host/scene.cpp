@@ -7,12 +7,14 @@
 #include "scene.hpp"
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
 #include <sstream>
 #include <stdexcept>
 
+#include "dedup_gpu.hpp"
 #include "json_mini.hpp"
 #include "obj_loader.hpp"
 #include "parallel.hpp"
@@ -353,9 +355,12 @@ void dedup_and_emit(CornerStage& st, ptb_scene& s, int threads) {
 
 }  // namespace
 
-static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unordered_map<std::string, uint32_t>& name_to_id) {
+// gpu_device >= 0: vertex de-duplication, numbering, normalisation and the repack into upload layout run on that GPU
+// (csrc/cuda/dedup.cu); the arrays are the same bits either way (tests/test_gpu_loader.py).
+static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unordered_map<std::string, uint32_t>& name_to_id, int gpu_device) {
     // src/scene.cpp:330-539
     const int threads = loader_threads();
+    const bool verbose = getenv("PTB_LOADER_VERBOSE") != nullptr;
     CornerStage st;
     VKeyHash hasher;
     for (const JsonValue& p : objects.arr) {
@@ -405,7 +410,7 @@ static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unor
         const size_t ntri = obj.tri_material.size();
         const size_t t0 = st.tangent.size();
         st.key.resize((t0 + ntri) * 3);
-        st.hash.resize((t0 + ntri) * 3);
+        if (gpu_device < 0) st.hash.resize((t0 + ntri) * 3);   // the GPU path hashes on the device
         st.tangent.resize(t0 + ntri);
         st.material.resize(t0 + ntri);
         const size_t g0 = s.nor_geom.size();
@@ -442,10 +447,22 @@ static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unor
                 for (int i = 0; i < 3; i++) {
                     VKey k = {{vpos[i].x, vpos[i].y, vpos[i].z, vnor[i].x, vnor[i].y, vnor[i].z, vuv[i].x, vuv[i].y}};
                     st.key[(t0 + f) * 3 + i] = k;
-                    st.hash[(t0 + f) * 3 + i] = (uint64_t)hasher(k);
+                    if (gpu_device < 0) st.hash[(t0 + f) * 3 + i] = (uint64_t)hasher(k);
                 }
             }
         });
+    }
+    const auto t_dedup = std::chrono::steady_clock::now();
+    auto elapsed_ms = [&t_dedup]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_dedup).count(); };
+    if (gpu_device >= 0) {
+        static_assert(sizeof(VKey) == 32 && sizeof(V3) == 12, "corner keys and tangents are uploaded as they lie");
+        GpuDedupTimes tm;
+        if (!st.material.empty())
+            gpu_dedup_pack(gpu_device, st.key[0].v, &st.tangent[0].x, st.material.data(), st.material.size(), s, &tm);
+        if (verbose)
+            fprintf(stderr, "ptb200: loader de-duplication + pack on GPU %d: %zu corners -> %zu vertices, %.1f ms (upload %.1f, device %.1f, download %.1f)\n",
+                    gpu_device, tm.corners, tm.vertices, elapsed_ms(), tm.upload_ms, tm.device_ms, tm.download_ms);
+        return;
     }
     dedup_and_emit(st, s, threads);
     // upload-time normalisation (src/wavefront_internal.cu:136-144): zero vectors become NaN, as there
@@ -459,9 +476,12 @@ static void load_objects(const JsonValue& objects, ptb_scene& s, const std::unor
             s.tangent[i] = f4{t.x, t.y, t.z, 0.0f};
         }
     });
+    if (verbose)
+        fprintf(stderr, "ptb200: loader de-duplication + pack on %d host threads: %zu corners -> %zu vertices, %.1f ms\n", threads, st.key.size(),
+                s.pos.size(), elapsed_ms());
 }
 
-void load_scene_json(const std::string& path, ptb_scene& s) {
+void load_scene_json(const std::string& path, ptb_scene& s, int gpu_device) {
     size_t dot = path.find_last_of('.');
     if (dot == std::string::npos || path.substr(dot) != ".json")
         throw std::runtime_error("Couldn't read from " + path + " (unknown extension)");   // src/scene.cpp:48-55
@@ -476,7 +496,7 @@ void load_scene_json(const std::string& path, ptb_scene& s) {
 
     std::unordered_map<std::string, uint32_t> name_to_id;
     if (data.contains("Materials")) load_materials(data.at("Materials"), s, name_to_id);
-    if (data.contains("Objects")) load_objects(data.at("Objects"), s, name_to_id);
+    if (data.contains("Objects")) load_objects(data.at("Objects"), s, name_to_id, gpu_device);
     if (data.contains("Camera")) {   // src/scene.cpp:541-577
         const JsonValue& c = data.at("Camera");
         s.camera.resolution[0] = (int)c.at("RES").at((size_t)0).number();

@@ -65,8 +65,9 @@ struct ptb_scene {
 
 namespace ptb {
 
-// Scene::loadFromJSON and friends (src/scene.cpp:83-631).  Throws std::runtime_error.
-void load_scene_json(const std::string& path, ptb_scene& out);
+// Scene::loadFromJSON and friends (src/scene.cpp:83-631).  Throws std::runtime_error.  gpu_device >= 0 runs the vertex
+// de-duplication and the repack into upload layout on that GPU (dedup_gpu.hpp); -1 keeps them on the host threads.
+void load_scene_json(const std::string& path, ptb_scene& out, int gpu_device = -1);
 // Scene::buildLightCDF (src/scene.cpp:579-631)
 void build_light_cdf(ptb_scene& s);
 // Scene::buildEnvMapAliasTable after the image is decoded (src/scene.cpp:194-299)

@@ -3,6 +3,7 @@
 #include <vector>
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -52,23 +53,44 @@ extern "C" {
 int ptb_abi_version(void) { return PTB_ABI_VERSION; }
 const char* ptb_last_error(void) { return g_last_error.c_str(); }
 
-int ptb_scene_load(const char* json_path, ptb_scene** out) {
-    if (!json_path || !out) return fail(PTB_ERR_INVALID, "ptb_scene_load: null argument");
+static int scene_load(const char* fn, const char* json_path, int gpu_device, ptb_scene** out) {
+    const std::string who(fn);
+    if (!json_path || !out) return fail(PTB_ERR_INVALID, who + ": null argument");
     *out = nullptr;
     std::string path(json_path);
     // Only .json scenes are accepted (src/scene.cpp:48-55)
-    if (path.size() < 5 || path.substr(path.size() - 5) != ".json") return fail(PTB_ERR_INVALID, "ptb_scene_load: not a .json scene: " + path);
+    if (path.size() < 5 || path.substr(path.size() - 5) != ".json") return fail(PTB_ERR_INVALID, who + ": not a .json scene: " + path);
     ptb_scene* s = new ptb_scene();
     try {
-        load_scene_json(path, *s);
+        load_scene_json(path, *s, gpu_device);
     } catch (const std::exception& e) {
         delete s;
         std::string msg = e.what();
-        int code = msg.find("unsupported") != std::string::npos ? PTB_ERR_UNSUPPORTED : msg.find("open") != std::string::npos ? PTB_ERR_IO : PTB_ERR_PARSE;
-        return fail(code, "ptb_scene_load: " + msg);
+        int code = msg.compare(0, 5, "cuda:") == 0                ? PTB_ERR_CUDA
+                   : msg.find("unsupported") != std::string::npos ? PTB_ERR_UNSUPPORTED
+                   : msg.find("open") != std::string::npos        ? PTB_ERR_IO
+                                                                  : PTB_ERR_PARSE;
+        return fail(code, who + ": " + msg);
     }
     *out = s;
     return PTB_OK;
+}
+
+int ptb_scene_load(const char* json_path, ptb_scene** out) {
+    // PTB_LOADER_GPU=<ordinal> routes callers that cannot change their call (the reference-side shim) through the GPU loader
+    int gpu_device = -1;
+    if (const char* e = getenv("PTB_LOADER_GPU")) {
+        char* end = nullptr;
+        long v = strtol(e, &end, 10);
+        if (end == e || *end || v < 0 || v > 1023) return fail(PTB_ERR_INVALID, std::string("ptb_scene_load: PTB_LOADER_GPU is not a device ordinal: ") + e);
+        gpu_device = (int)v;
+    }
+    return scene_load("ptb_scene_load", json_path, gpu_device, out);
+}
+
+int ptb_scene_load_device(const char* json_path, int32_t device, ptb_scene** out) {
+    if (device < 0) return fail(PTB_ERR_INVALID, "ptb_scene_load_device: negative device ordinal");
+    return scene_load("ptb_scene_load_device", json_path, device, out);
 }
 
 int ptb_scene_from_arrays(const float* pos, const float* nor, const float* uv, const float* tangent, int32_t num_vertices,

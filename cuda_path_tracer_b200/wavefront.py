@@ -40,10 +40,14 @@ def _fetch(getter, handle, spec):
 class Scene:
     """`class Scene` of the reference (src/scene.h:51-92): same scene.json schema and semantics."""
 
-    def __init__(self, filename=None, _handle=None):
+    def __init__(self, filename=None, _handle=None, device=None):
+        """device: a GPU ordinal runs the vertex de-duplication and the repack into upload layout there
+        (ptb_scene_load_device); None keeps them on the host threads.  Same scene, bit for bit."""
         self._h = C.c_void_p()
         if _handle is not None:
             self._h = _handle
+        elif device is not None:
+            check(lib.ptb_scene_load_device(str(filename).encode(), int(device), C.byref(self._h)))
         else:
             check(lib.ptb_scene_load(str(filename).encode(), C.byref(self._h)))
 

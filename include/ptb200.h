@@ -77,6 +77,14 @@ int ptb_device_count(void);
  * semantics, material-id order, vertex de-duplication order, light CDF and env alias table
  * (src/scene.cpp:83-631).  Pure host work; textures are uploaded by ptb_init. */
 int ptb_scene_load(const char* json_path, ptb_scene** out);
+/* ptb_scene_load with the vertex de-duplication (the unordered_map<Vertex,int> walk of src/scene.cpp:330-539, numbering at
+ * :525-532) and the repack into upload layout with normalised normals / tangents (src/wavefront_internal.cu:118-167) done on GPU
+ * `device`: every corner inserts itself into a device hash table that keeps the minimum corner index per key class, an exclusive
+ * scan of the first-occurrence flags in file order numbers the vertices.  The resulting scene is bit-identical to
+ * ptb_scene_load's.  PTB_ERR_CUDA when the device cannot be used (no fall-back to the host path); at most 2^30 triangle
+ * corners.  Setting PTB_LOADER_GPU=<ordinal> in the environment makes ptb_scene_load itself take this route.
+ * PTB_LOADER_VERBOSE=1 prints the stage's time on stderr for either route. */
+int ptb_scene_load_device(const char* json_path, int32_t device, ptb_scene** out);
 
 /* Direct SoA injection for synthetic meshes (what WavefrontPathTracerState::initSceneGeometry
  * builds from a Scene, src/wavefront_internal.cu:118-167).

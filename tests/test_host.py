@@ -236,6 +236,10 @@ def test_no_cpu_fallback(tmp_path):
     with pytest.raises(capi.PtbError) as e:
         ptb.build_lbvh(s.array("pos"), s.array("indices_matid"))
     assert e.value.code == capi.ERR_CUDA
+    # the GPU loader does not quietly become the host loader
+    with pytest.raises(capi.PtbError) as e:
+        ptb.Scene(scenegen.cornell(str(tmp_path / "c2"), res=(8, 8)), device=0)
+    assert e.value.code == capi.ERR_CUDA
 
 
 def test_product_does_not_touch_oracle():

@@ -28,6 +28,24 @@ def checksum(scene):
     return "%016x" % int(h)
 
 
+def load_with_stage_line(path, device=None):
+    """(scene, seconds, the loader's own PTB_LOADER_VERBOSE line about its de-duplication + pack stage)"""
+    import tempfile
+    os.environ["PTB_LOADER_VERBOSE"] = "1"
+    sys.stderr.flush()
+    keep = os.dup(2)
+    with tempfile.TemporaryFile() as f:
+        os.dup2(f.fileno(), 2)
+        try:
+            t0 = time.perf_counter(); s = ptb.Scene(path, device=device); dt = time.perf_counter() - t0
+        finally:
+            os.dup2(keep, 2); os.close(keep)
+            os.environ.pop("PTB_LOADER_VERBOSE", None)
+        f.seek(0)
+        lines = [l for l in f.read().decode(errors="replace").splitlines() if "de-duplication" in l]
+    return s, dt, (lines[-1].replace("ptb200: ", "") if lines else "")
+
+
 def main():
     scale = float(sys.argv[1]) if len(sys.argv) > 1 else 3.8
     out_dir = sys.argv[2] if len(sys.argv) > 2 else "/tmp/ingest_scene"
@@ -47,6 +65,14 @@ def main():
             res["checksums"].append(checksum(c)); c.free()
         s.free()
     os.environ.pop("PTB_LOADER_THREADS", None)
+    s, dt, line = load_with_stage_line(path)
+    res["host_stage"] = line; s.free()
+    if ptb.capi.lib.ptb_device_count() > 0:
+        # de-duplication + repack on GPU 0 (ptb_scene_load_device): the first call pays for the CUDA context, the second does not
+        for label in ("load_gpu_first_s", "load_gpu_s"):
+            s, dt, line = load_with_stage_line(path, device=0)
+            res[label] = round(dt, 3); res["gpu_stage"] = line
+            res["checksums"].append(checksum(s)); s.free()
     if os.path.exists(REFDUMP):
         q = subprocess.run([REFDUMP, path, "/tmp/ingest_ref", "--load-only"], capture_output=True, text=True)
         for l in q.stdout.splitlines():
