@@ -178,21 +178,23 @@ struct TexturesDev {
 // the slot by TileMap, so it is not stored.
 // Storage is three 32-byte records per slot, one per WRITER, so that every store of a stage is a whole 32-byte sector (a
 // partial-sector store costs a fill read plus a whole-sector write-back; the round-1 layout had three of them per ray in
-// RayCast and two per path in Shade -- 2.8x the algorithmic DRAM bytes):
-//   ray  [2*slot] = ray_ori (xyz, 0)            ray  [2*slot+1] = (dir.xyz, FLT_MAX)     written by RayGen / Shade, read by RayCast
-//   hit  [2*slot] = (t, u, v, bits(prim))       hit  [2*slot+1] = (bits(mat), 0, 0, 0)   written by RayCast (t = -1, prim = -1: miss)
-//   state[2*slot] = throughput_pdf              state[2*slot+1] = (bits(remaining_bounces), bits(rng_state), 0, 0)
+// RayCast and two per path in Shade -- 2.8x the algorithmic DRAM bytes).  The ray and the state record of a slot are the two
+// halves of ONE 64-byte block: HBM moves 64 bytes per access (a scattered 32-byte record costs 64 bytes of DRAM traffic either
+// way: measured, profiles/r02_raycast_notes.md section 3), RayGen and Shade write both halves, RayCast + Logic and Shade read both.
+//   ray  = rs[4*slot]   = ray_ori (xyz, 0)      rs[4*slot+1] = (dir.xyz, FLT_MAX)        written by RayGen / Shade, read by RayCast
+//   state= rs[4*slot+2] = throughput_pdf        rs[4*slot+3] = (bits(remaining_bounces), bits(rng_state), 0, 0)
 //                                                                                        written by RayGen / Shade (Logic: remaining = -1)
+//   hit  [2*slot] = (t, u, v, bits(prim))       hit  [2*slot+1] = (bits(mat), 0, 0, 0)   written by RayCast (t = -1, prim = -1: miss)
 // The reference's fields map onto them as: ray_dir_dist.w after a trace = hit.t; hit_normal = (hit.u, hit.v, 0, 0); hit_geom_id =
 // hit.prim; material_id = hit.mat (ptb_get_path_field assembles these views).  Members with operator[] keep the reference's names.
-struct PoolF4 {                  // every second float4 of an interleaved array
+struct PoolF4 {                  // one float4 of every 64-byte ray + state block
     float4* base;
-    __device__ __forceinline__ float4& operator[](int i) const { return base[2 * (size_t)i]; }
+    __device__ __forceinline__ float4& operator[](int i) const { return base[4 * (size_t)i]; }
 };
 template <typename T>
-struct PoolI {                   // one 32-bit word of the 32-byte `state` records
+struct PoolI {                   // one 32-bit word of every 64-byte ray + state block
     T* base;
-    __device__ __forceinline__ T& operator[](int i) const { return base[8 * (size_t)i]; }
+    __device__ __forceinline__ T& operator[](int i) const { return base[16 * (size_t)i]; }
 };
 // One 32-byte store / load of a whole record (sm_100 STG.256 / LDG.256): a full sector, no partial write.
 __device__ __forceinline__ void stg256(float4* p, float4 a, float4 b) {
@@ -210,9 +212,10 @@ struct PathPool {
     PoolF4 throughput_pdf;
     PoolI<int> remaining_bounces;
     PoolI<uint32_t> rng_state;
-    float4* ray;                 // [2 * P]
+    float4* rs;                  // [4 * P]: ray (2 float4) + state (2 float4) per slot
     float4* hit;                 // [2 * P]
-    float4* state;               // [2 * P]
+    __device__ __forceinline__ float4* ray_record(int slot) const { return rs + 4 * (size_t)slot; }
+    __device__ __forceinline__ float4* state_record(int slot) const { return rs + 4 * (size_t)slot + 2; }
     __device__ __forceinline__ void store_hit(int slot, float t, float u, float v, int prim, int mat) const {
         stg256(hit + 2 * (size_t)slot, make_float4(t, u, v, __int_as_float(prim)), make_float4(__int_as_float(mat), 0.0f, 0.0f, 0.0f));
     }
@@ -224,11 +227,11 @@ struct PathPool {
         return h;
     }
     __device__ __forceinline__ void store_state(int slot, float4 tp, int remaining, uint32_t rng) const {
-        stg256(state + 2 * (size_t)slot, tp, make_float4(__int_as_float(remaining), __uint_as_float(rng), 0.0f, 0.0f));
+        stg256(state_record(slot), tp, make_float4(__int_as_float(remaining), __uint_as_float(rng), 0.0f, 0.0f));
     }
     __device__ __forceinline__ void load_state(int slot, float4& tp, int& remaining, uint32_t& rng) const {
         float4 b;
-        ldg256_rw(state + 2 * (size_t)slot, tp, b);
+        ldg256_rw(state_record(slot), tp, b);
         remaining = __float_as_int(b.x); rng = __float_as_uint(b.y);
     }
 };

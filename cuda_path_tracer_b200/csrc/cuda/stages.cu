@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(kThreads) k_raygen(FrameDev f) {
     Vec3 dir = normalize3(view
         + right * f.cam.pixel_length[0] * ((float)x + jx - (float)f.cam.res_x * 0.5f)
         - up * f.cam.pixel_length[1] * ((float)y + jy - (float)f.cam.res_y * 0.5f));
-    stg256(f.pool.ray + 2 * (size_t)slot, make_float4(f.cam.pos[0], f.cam.pos[1], f.cam.pos[2], 0.0f), make_float4(dir.x, dir.y, dir.z, FLT_MAX));
+    stg256(f.pool.ray_record(slot), make_float4(f.cam.pos[0], f.cam.pos[1], f.cam.pos[2], 0.0f), make_float4(dir.x, dir.y, dir.z, FLT_MAX));
     // the reference also resets hit_geom_id / material_id to -1 here (src/kernels/ray_gen.cu:68-69); the hit record is only defined
     // after a trace, and ptb_get_path_field reports -1 until then
     f.pool.store_state(slot, make_float4(1.0f, 1.0f, 1.0f, 0.0f), f.trace_depth, seed);
@@ -93,7 +93,7 @@ struct ShadeOut {
 template <int TYPE, bool ENV>
 __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut& out) {
     float4 oo, dd;                                        // three whole records: ray, hit, state
-    ldg256_rw(f.pool.ray + 2 * (size_t)idx, oo, dd);
+    ldg256_rw(f.pool.ray_record(idx), oo, dd);
     const HitRecord hr = f.pool.load_hit(idx);
     float4 tp; int remaining; uint32_t seed;
     f.pool.load_state(idx, tp, remaining, seed);
@@ -206,7 +206,7 @@ __device__ __forceinline__ void shade_path(const FrameDev& f, int idx, ShadeOut&
         }
         if (alive) {
             tp = make_float4(throughput.x, throughput.y, throughput.z, next_pdf);
-            stg256(f.pool.ray + 2 * (size_t)idx,
+            stg256(f.pool.ray_record(idx),
                    make_float4(P.x + bias_n.x * PTB_EPSILON, P.y + bias_n.y * PTB_EPSILON, P.z + bias_n.z * PTB_EPSILON, 0.0f),
                    make_float4(next_dir.x, next_dir.y, next_dir.z, FLT_MAX));
             out.push_ext = true;

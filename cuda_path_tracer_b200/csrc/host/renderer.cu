@@ -455,14 +455,13 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     f.num_paths = (int)P;
     f.trace_depth = cfg.trace_depth > 0 ? cfg.trace_depth : scene->trace_depth;
     if (f.trace_depth < 1) f.trace_depth = 1;
-    TRY(dev_alloc(r, f.pool.ray, 2 * P));
+    TRY(dev_alloc(r, f.pool.rs, 4 * P));
     TRY(dev_alloc(r, f.pool.hit, 2 * P));
-    TRY(dev_alloc(r, f.pool.state, 2 * P));
-    f.pool.ray_ori.base = f.pool.ray;
-    f.pool.ray_dir_dist.base = f.pool.ray + 1;
-    f.pool.throughput_pdf.base = f.pool.state;
-    f.pool.remaining_bounces.base = reinterpret_cast<int*>(f.pool.state + 1) + 0;
-    f.pool.rng_state.base = reinterpret_cast<uint32_t*>(f.pool.state + 1) + 1;
+    f.pool.ray_ori.base = f.pool.rs;
+    f.pool.ray_dir_dist.base = f.pool.rs + 1;
+    f.pool.throughput_pdf.base = f.pool.rs + 2;
+    f.pool.remaining_bounces.base = reinterpret_cast<int*>(f.pool.rs + 3) + 0;
+    f.pool.rng_state.base = reinterpret_cast<uint32_t*>(f.pool.rs + 3) + 1;
     TRY(dev_alloc(r, f.shadow.ray_ori_tmax, nee_factor * P));
     TRY(dev_alloc(r, f.shadow.ray_dir, nee_factor * P));
     TRY(dev_alloc(r, f.shadow.radiance, nee_factor * P));
@@ -483,9 +482,9 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
     TRYCU(cudaMemsetAsync(f.direct, 0, nee_factor * 3 * P * sizeof(float), r->stream));
     TRYCU(cudaMemsetAsync(f.indirect, 0, 3 * P * sizeof(float), r->stream));
     // InitPathPoolKernel (src/pathtrace_wavefront.cu:183-190): every slot starts dead
-    TRYCU(cudaMemsetAsync(f.pool.state, 0xff, 2 * P * sizeof(float4), r->stream));   // remaining_bounces = -1
+    TRYCU(cudaMemsetAsync(f.pool.rs, 0, 4 * P * sizeof(float4), r->stream));
+    TRYCU(cudaMemset2DAsync(f.pool.rs + 2, 64, 0xff, 32, P, r->stream));             // state halves: remaining_bounces = -1
     TRYCU(cudaMemsetAsync(f.pool.hit, 0xff, 2 * P * sizeof(float4), r->stream));     // hit_geom_id = material_id = -1
-    TRYCU(cudaMemsetAsync(f.pool.ray, 0, 2 * P * sizeof(float4), r->stream));
 
     // ---- first-bounce G-buffer (initSVGF buffers, src/wavefront_internal.cu:286-300), on request
     f.view_proj = nullptr;
@@ -982,20 +981,20 @@ int ptb_get_shadow_queue(ptb_renderer* r, float* ori_tmax4, float* dir4, float* 
 int ptb_get_path_field(ptb_renderer* r, int32_t field, void* dst, size_t bytes) {
     if (!r || !dst) return fail(PTB_ERR_INVALID, "ptb_get_path_field: null argument");
     CU(cudaSetDevice(r->device));
-    // The reference's PathState fields as VIEWS of the three 32-byte records of a slot (common.cuh): src / pitch select a word
-    // range of a record; ray_dir_dist.w and hit_normal are assembled below.
+    // The reference's PathState fields as VIEWS of the records of a slot (common.cuh: a 64-byte ray + state block, a 32-byte hit
+    // record): src / pitch select a word range of a record; ray_dir_dist.w and hit_normal are assembled below.
     const char* src;
-    size_t elem, pitch = 32;
+    size_t elem, pitch = 64;
     const PathPool& pool = r->frame.pool;
     switch (field) {
-        case PTB_PF_RAY_ORI: src = (const char*)pool.ray; elem = 16; break;
-        case PTB_PF_RAY_DIR_DIST: src = (const char*)(pool.ray + 1); elem = 16; break;
-        case PTB_PF_HIT_UV: src = (const char*)pool.hit; elem = 16; break;                 // (t, u, v, prim) -> (u, v, 0, 0) below
-        case PTB_PF_THROUGHPUT_PDF: src = (const char*)pool.state; elem = 16; break;
-        case PTB_PF_HIT_GEOM_ID: src = (const char*)pool.hit + 12; elem = 4; break;
-        case PTB_PF_MATERIAL_ID: src = (const char*)pool.hit + 16; elem = 4; break;
-        case PTB_PF_REMAINING_BOUNCES: src = (const char*)pool.state + 16; elem = 4; break;
-        case PTB_PF_RNG_STATE: src = (const char*)pool.state + 20; elem = 4; break;
+        case PTB_PF_RAY_ORI: src = (const char*)pool.rs; elem = 16; break;
+        case PTB_PF_RAY_DIR_DIST: src = (const char*)(pool.rs + 1); elem = 16; break;
+        case PTB_PF_HIT_UV: src = (const char*)pool.hit; elem = 16; pitch = 32; break;     // (t, u, v, prim) -> (u, v, 0, 0) below
+        case PTB_PF_THROUGHPUT_PDF: src = (const char*)(pool.rs + 2); elem = 16; break;
+        case PTB_PF_HIT_GEOM_ID: src = (const char*)pool.hit + 12; elem = 4; pitch = 32; break;
+        case PTB_PF_MATERIAL_ID: src = (const char*)pool.hit + 16; elem = 4; pitch = 32; break;
+        case PTB_PF_REMAINING_BOUNCES: src = (const char*)(pool.rs + 3); elem = 4; break;
+        case PTB_PF_RNG_STATE: src = (const char*)(pool.rs + 3) + 4; elem = 4; break;
         default: return fail(PTB_ERR_INVALID, "ptb_get_path_field: unknown field");
     }
     const TileMap& tm = r->frame.tile;
