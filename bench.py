@@ -15,6 +15,10 @@ iterations on rank 0 (scalar keys config.*_bit_identical / *_max_rel_err):
     r+1, r+1+N, ...; a step is N samples per pixel;
   * tile partition (config.tile_*, strong scaling): ONE frame per step cut into N interleaved 8-row stripe sets;
   * hybrid (config.hybrid_*): G tile groups x N/G sample groups.
+With N > 1 the run also renders BASELINE configs 5 (262,279-triangle textured scene + HDR sky, 3840x2160, 64 spp) and 4
+(10,000,000 triangles, 1920x1080, 4 spp) as whole jobs over the N GPUs in the partitions their sample counts allow
+(config.config5_* / config.config4_*: job ms, Mpaths/s, speed-up over ONE renderer doing the same job on rank 0, bit-identity /
+max relative error against that renderer's frame).
 Every secondary figure is a flat scalar key (the driver's record keeps scalars only).
 """
 import argparse
@@ -298,20 +302,23 @@ def main():
     class Partition:
         """One way of cutting the work over the ranks, through the peer-store gather (or, without peer access, NCCL)."""
 
-        def __init__(self, tile_groups):
+        def __init__(self, tile_groups, scene_=None, res=None, out=None):
             self.G = tile_groups
             self.S = world // tile_groups
+            self.W, self.H = res or (W, H)
+            self.P = self.W * self.H
+            self.out = out_frame if out is None else out
             self.peer = None
             try:
-                self.peer = multigpu.PeerFrame(W, H, dist, local_rank, tile_groups=tile_groups, stripe_rows=stripe)
+                self.peer = multigpu.PeerFrame(self.W, self.H, dist, local_rank, tile_groups=tile_groups, stripe_rows=stripe)
                 kw = self.peer.renderer_kwargs()
             except multigpu.PeerUnavailable:
                 kw = dict(rank=rank % self.G, world=self.G, stripe_rows=stripe)
-                self.nccl_tile = multigpu.FrameGather(W, H, stripe, dist, device="cuda") if self.S == 1 else None
-                self.nccl_sum = multigpu.SampleReduce(W, H, dist, device="cuda") if self.G == 1 else None
+                self.nccl_tile = multigpu.FrameGather(self.W, self.H, stripe, dist, device="cuda") if self.S == 1 else None
+                self.nccl_sum = multigpu.SampleReduce(self.W, self.H, dist, device="cuda") if self.G == 1 else None
                 if self.nccl_tile is None and self.nccl_sum is None:
                     raise
-            self.r = ptb.Renderer(scene, device=local_rank, **kw)
+            self.r = ptb.Renderer(scene if scene_ is None else scene_, device=local_rank, **kw)
             self.r.set_stream(stream.cuda_stream)
             self.combines = 0
 
@@ -324,9 +331,9 @@ def main():
             if self.peer is not None:
                 self.peer.submit(self.r, k)
                 if rank == 0:
-                    self.peer.combine_device(out_frame.data_ptr(), k + 1, capi.IMG_MEAN_RGB32F, stream.cuda_stream, k)
+                    self.peer.combine_device(self.out.data_ptr(), k + 1, capi.IMG_MEAN_RGB32F, stream.cuda_stream, k)
                     self.combines += 1
-                return out_frame
+                return self.out
             if self.nccl_tile is not None:
                 self.r.resolve_device(self.nccl_tile.tile.data_ptr(), k + 1)
                 return self.nccl_tile.gather()
@@ -341,7 +348,7 @@ def main():
             e0.record(stream)
             ref_renderer.render(1, n)
             e1.record(stream)
-            ref = torch.empty((P, 3), dtype=torch.float32, device="cuda")
+            ref = torch.empty((self.P, 3), dtype=torch.float32, device="cuda")
             ref_renderer.resolve_device(ref.data_ptr(), n)
             torch.cuda.synchronize()
             a, b = frame.cpu().numpy(), ref.cpu().numpy()
@@ -466,6 +473,65 @@ def main():
         torch.cuda.synchronize()
         barrier()
         e2e_s = allmax(time.perf_counter() - t0)
+        # ---- N > 1: BASELINE configs 5 and 4 (the multi-GPU cases of north_star) as whole jobs, same gather, same checks
+        if world > 1 and not args.no_extras:
+            try:
+                from cuda_path_tracer_b200 import scenegen as sg
+                for tag, spp, res in (("config5", 64, (3840, 2160)), ("config4", 4, (1920, 1080))):
+                    if tag == "config5":
+                        sdir = "/tmp/ptb_bench_sponza"
+                        if rank == 0:
+                            sg.sponza(sdir, res=res)
+                        barrier()
+                        sc = ptb.Scene(os.path.join(sdir, "scene.json"))
+                        extra[tag + "_workload"] = "262279-triangle textured scene + HDR sky, 3840x2160, 8 bounces, 64 spp (one job)"
+                    else:
+                        pos, nor, idx, mat = sg.heightfield_arrays(10_000_000)
+                        sc = ptb.Scene.from_arrays(pos, nor, idx, mat, sg.stress_materials(), sg.stress_camera(res))
+                        del pos, nor, idx, mat
+                        extra[tag + "_workload"] = "10000000-triangle height field, 1920x1080, 8 bounces, 4 spp (one job)"
+                    Px = res[0] * res[1]
+                    outx = torch.empty((Px, 3), dtype=torch.float32, device="cuda")
+                    refx = None
+                    if rank == 0:
+                        refx = ptb.Renderer(sc, device=local_rank)
+                        refx.set_stream(stream.cuda_stream)
+                        refx.render(1, 2)                                  # warm-up of the one-GPU comparison render
+                        sx = refx.stats()
+                        extra[tag + "_lbvh_build_ms"] = round(sx.lbvh_build_ms, 3)
+                        extra[tag + "_lbvh_max_depth"] = sx.lbvh_max_depth
+                    for label, G in (("tile", world), ("hybrid", 2), ("sample", 1)):
+                        S = world // G
+                        if G > world or world % G or spp % S or (label == "hybrid" and (world < 4 or G == world)):
+                            continue
+                        px = Partition(G, sc, res, outx)
+                        steps = spp // S
+                        for timed_run in (False, True):                    # the whole job twice; the second one is timed
+                            barrier()
+                            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                            e0.record(stream)
+                            for k in range(steps):
+                                frame = px.step(k)
+                            e1.record(stream)
+                            barrier()
+                            job_ms = allmax(e0.elapsed_time(e1))
+                        key = f"{tag}_{label}"
+                        extra[key + "_groups"] = f"{G} tile groups x {S} sample groups"
+                        extra[key + "_job_ms"] = round(job_ms, 3)
+                        extra[key + "_mpaths_per_s"] = round(Px * spp / job_ms / 1e3, 1)
+                        if refx is not None:
+                            same, rel, one_ms = px.check(frame, steps, refx)
+                            extra[key + "_bit_identical"] = same
+                            extra[key + "_max_rel_err"] = rel
+                            extra[tag + "_one_gpu_job_ms"] = round(one_ms * spp, 3)
+                            extra[key + "_speedup_vs_1gpu"] = round(one_ms * spp / job_ms, 3)
+                        px.free()
+                    if refx is not None:
+                        refx.free()
+                    sc.free()
+                    del outx
+            except Exception as e:                                         # the headline line must survive a failure here
+                extra["other_configs_error"] = repr(e)[:300]
         roof = shadow = cpu = None
         if not args.no_extras and world == 1:
             roof, shadow, cpu = roofline_and_cpu(r, scene, world, rank, rays / (args.steps * P * world), sm_count, (clk or {}).get("sm_max_mhz"))
