@@ -57,11 +57,21 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, PTB_RC_MINBLOCKS) k_trace_exte
 // every decision that shapes it is warp-uniform (ballots at the two converged points), so the lanes of a warp reconverge
 // after every traversal step whatever their rays do.
 struct StackShared {                         // the whole column in shared memory
-    static constexpr int kShared = PTB_EXT_STACK;
-    int* col;
-    __device__ __forceinline__ explicit StackShared(int* c) : col(c) {}
-    __device__ __forceinline__ int get(int i) const { return col[i * PTB_RC_THREADS]; }
-    __device__ __forceinline__ void set(int i, int v) { col[i * PTB_RC_THREADS] = v; }
+    static constexpr int kShared = PTB_EXT_STACK + PTB_WIDE_PUSHES;
+    // the column's address in the shared window, held in ONE register the compiler cannot re-derive: it would otherwise rebuild it
+    // from %tid and the CTA's window base (two S2R, three more instructions) at every push
+    unsigned base;
+    __device__ __forceinline__ explicit StackShared(int* c) : base((unsigned)__cvta_generic_to_shared(c)) {
+        asm volatile("mov.u32 %0, %0;" : "+r"(base));
+    }
+    __device__ __forceinline__ int get(int i) const {
+        int v;
+        asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(base + (unsigned)i * (PTB_RC_THREADS * 4u)) : "memory");
+        return v;
+    }
+    __device__ __forceinline__ void set(int i, int v) {
+        asm volatile("st.shared.s32 [%0], %1;" :: "r"(base + (unsigned)i * (PTB_RC_THREADS * 4u)), "r"(v) : "memory");
+    }
 };
 template <int SH>
 struct StackHybrid {                         // the SH entries nearest the root in shared memory, deeper ones in local memory
@@ -159,7 +169,7 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, (SHARED && STACK <= 32) ? PTB_
 // levels deep (the stack column is PTB_EXT_STACK entries).  A ray the wide walk cannot decide is re-walked on the fp32 records.
 template <int MINB, int STEPS>
 __global__ void __launch_bounds__(PTB_RC_THREADS, MINB) k_trace_shadow_pl(FrameDev f, int bounce, int refill) {
-    __shared__ int stack[PTB_EXT_STACK * PTB_RC_THREADS];
+    __shared__ int stack[StackShared::kShared * PTB_RC_THREADS];
     int* ctr = f.ctr + bounce * CTR_STRIDE;
     const int count = ctr[CTR_SHADOW];
     int* cursor = &ctr[CTR_WORK_SHADOW];
@@ -196,7 +206,7 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, MINB) k_trace_shadow_pl(FrameD
         } while (n_done < want);
         if (ray >= 0 && !w.busy()) {
             int res = w.result;
-            if (res < 0) res = trace_any<PTB_EXT_STACK>(f.bvh, w.r.o, w.r.d, w.tmax, st.col, PTB_RC_THREADS);
+            if (res < 0) res = trace_any<PTB_EXT_STACK>(f.bvh, w.r.o, w.r.d, w.tmax, stack + threadIdx.x, PTB_RC_THREADS);
             if (res == 0) {   // visible: AtomicAddVec3(&d_direct_image[pixel], radiance), src/kernels/ray_cast.cu:193-199
                 int slot = __ldg(&f.shadow.slot[ray]);
                 float4 rad = __ldg(&f.shadow.radiance[ray]);

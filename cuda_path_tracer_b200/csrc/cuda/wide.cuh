@@ -24,6 +24,7 @@ namespace ptb {
 
 #define PTB_WIDE_SLACK 1.00001f
 #define PTB_WIDE_STACK 32
+#define PTB_WIDE_PUSHES 3          /* spare stack entries of the persistent-lane walks: a node visit pushes at most three children */
 #define PTB_WIDE_SEL_LO 0x7104u   /* PRMT selectors, see wide_plane() */
 #define PTB_WIDE_SEL_HI 0x7324u
 
@@ -54,11 +55,16 @@ __device__ __forceinline__ WideRay wide_setup(const BvhDev& bvh, Vec3 o, Vec3 d)
 
 // A child's word holds lo | hi << 16 (15-bit steps).  One PRMT turns either half into the float 32768 + q:
 // bytes (0, q.lo, q.hi, 0x47); the selector picks the half, so the ray's octant costs no extra instruction.
+// (prmt.b32 itself: __byte_perm() masks the selector with 0x7777 first, one more ALU instruction per plane when the selector
+// comes out of a register.)
 __device__ __forceinline__ float wide_plane(unsigned word, unsigned sel) {
-    return __uint_as_float(__byte_perm(word, 0x47000000u, sel));
+    unsigned r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(word), "r"(0x47000000u), "r"(sel));
+    return __uint_as_float(r);
 }
 
 // Entry distances of the four children (max(0, t_near)), or -1 where the ray misses the box or enters beyond t_limit.
+template <bool MISS_IS_MAX = false>
 __device__ __forceinline__ void wide_test(const WideRay& r, const uint4& qx, const uint4& qy, const uint4& qz, float t_limit, float t[4]) {
     const unsigned far_x = r.near_x ^ 0x0220u, far_y = r.near_y ^ 0x0220u, far_z = r.near_z ^ 0x0220u;
     const unsigned wx[4] = {qx.x, qx.y, qx.z, qx.w}, wy[4] = {qy.x, qy.y, qy.z, qy.w}, wz[4] = {qz.x, qz.y, qz.z, qz.w};
@@ -70,7 +76,7 @@ __device__ __forceinline__ void wide_test(const WideRay& r, const uint4& qx, con
                          fmaf(wide_plane(wz[k], far_z), r.iqz, r.bz));
         tn = fmaxf(tn, 0.0f);
         tf = fminf(tf, t_limit);
-        t[k] = (tn <= tf) ? tn : -1.0f;
+        t[k] = (tn <= tf) ? tn : (MISS_IS_MAX ? FLT_MAX : -1.0f);     // MISS_IS_MAX: misses sort last in the closest-hit walks
     }
 }
 
@@ -352,16 +358,15 @@ struct WalkWide {
     WideRay r;
     float t, u, v, second;                    // best hit (t = FLT_MAX: none), nearest other accepted candidate
     int leaf;
-    int node, sp;
-    bool bad;
+    int node, sp;                             // second < 0: the walk cannot vouch for its result (bad reciprocal, stack overflow)
     __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
     __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
     __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o, Vec3 d) {
         r = wide_setup(bvh, o, d);
         t = FLT_MAX; u = 0.0f; v = 0.0f; second = FLT_MAX; leaf = -1;
         sp = 0;
-        bad = !r.ok;
-        node = bad ? PTB_NODE_NONE : 0;
+        if (!r.ok) second = -1.0f;
+        node = r.ok ? 0 : PTB_NODE_NONE;
     }
     template <class STACK>
     __device__ __forceinline__ void step(const BvhDev& bvh, STACK& st) {
@@ -375,17 +380,19 @@ struct WalkWide {
             const uint4 qz = make_uint4(__float_as_uint(b.a.x), __float_as_uint(b.a.y), __float_as_uint(b.a.z), __float_as_uint(b.a.w));
             int lnk[4] = {__float_as_int(b.b.x), __float_as_int(b.b.y), __float_as_int(b.b.z), __float_as_int(b.b.w)};
             float key[4];
-            wide_test(r, qx, qy, qz, limit, key);
-#pragma unroll
-            for (int k = 0; k < 4; k++) if (key[k] < 0.0f) key[k] = FLT_MAX;     // misses sort last
-            PTB_WIDE_CSWAP(0, 1) PTB_WIDE_CSWAP(2, 3) PTB_WIDE_CSWAP(0, 2) PTB_WIDE_CSWAP(1, 3) PTB_WIDE_CSWAP(1, 2)
+            wide_test<true>(r, qx, qy, qz, limit, key);
+            // nearest child first; the order of the other three decides almost nothing (3 % of the popped nodes could be
+            // culled by their entry distance, profiles/r02_raycast_notes.md), so the network stops once key[0] is the minimum
+            PTB_WIDE_CSWAP(0, 1) PTB_WIDE_CSWAP(2, 3) PTB_WIDE_CSWAP(0, 2)
+#ifdef PTB_WIDE_FULLSORT
+            PTB_WIDE_CSWAP(1, 3) PTB_WIDE_CSWAP(1, 2)
+#endif
+            // the column has PTB_WIDE_PUSHES spare entries: one overflow check per visit instead of one per push
 #pragma unroll
             for (int k = 3; k >= 1; k--) {
-                if (key[k] != FLT_MAX) {
-                    if (sp < PTB_WIDE_STACK) st.set(sp++, lnk[k]);
-                    else bad = true;
-                }
+                if (key[k] != FLT_MAX) { st.set(sp, lnk[k]); sp++; }
             }
+            if (sp > PTB_WIDE_STACK) { sp = PTB_WIDE_STACK; second = -1.0f; }   // entries dropped: finish() re-walks
             node = (key[0] != FLT_MAX) ? lnk[0] : PTB_NODE_NONE;
         } else {
             const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
@@ -407,11 +414,10 @@ struct WalkWide {
             }
             node = PTB_NODE_NONE;
         }
-        if (bad) { node = PTB_NODE_NONE; sp = 0; }
     }
     template <class STACK>
     __device__ __forceinline__ Hit finish(const BvhDev& bvh, STACK& st) {
-        const bool ambiguous = bad || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
+        const bool ambiguous = second < 0.0f || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
         if (ambiguous) {
             WalkBinary w;
             w.init(bvh, r.o, r.d);
@@ -461,10 +467,10 @@ struct WalkAnyWide {
             for (int k = 0; k < 4; k++) {
                 if (t[k] >= 0.0f) {
                     if (node == PTB_NODE_NONE) node = lnk[k];
-                    else if (sp < PTB_WIDE_STACK) st.set(sp++, lnk[k]);
-                    else result = -1;
+                    else { st.set(sp, lnk[k]); sp++; }
                 }
             }
+            if (sp > PTB_WIDE_STACK) result = -1;                       // PTB_WIDE_PUSHES spare entries took the excess
         } else {
             const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
             F8 ab = ldg256(tp);
