@@ -185,7 +185,7 @@ def roofline_and_cpu(r, scene, n_gpus, rank, stats_rays_per_path, sm_count, sm_m
     else:
         peak, peak_src = 7700.0, "fallback nominal HBM3e figure (MEASURED_PEAKS.json absent)"
     # ncu figures of the committed capture, only while the kernel sources are the captured ones
-    traffic = traffic_src = issue_frac = lanes = None
+    traffic = traffic_src = issue_frac = lanes = traffic_note = None
     tpath = os.path.join(ROOT, "profiles", "raycast_traffic.json")
     if os.path.exists(tpath):
         prof = json.load(open(tpath))
@@ -196,11 +196,12 @@ def roofline_and_cpu(r, scene, n_gpus, rank, stats_rays_per_path, sm_count, sm_m
             if wi and len(wi) == DEPTH and sm_count and sm_mhz:
                 issue_frac = round(sum(wi) / (ext["ms"] * 1e-3) / (sm_count * 4 * sm_mhz * 1e6), 3)
             lanes = prof.get("active_lanes_mean")
+            traffic_note = prof.get("note")
         else:
             traffic_src = "committed ncu capture is of other kernel sources: not reported"
     achieved = ext["bytes"] / (ext["ms"] * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": "k_trace_extension", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5),
-            "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "launches_per_step": DEPTH, "avg_launch_ms": round(ext["ms"] / DEPTH, 4),
+            "traffic": traffic, "traffic_source": traffic_src, "traffic_note": traffic_note, "peak_source": peak_src, "launches_per_step": DEPTH, "avg_launch_ms": round(ext["ms"] / DEPTH, 4),
             "avg_launch_ms_cold": round(ext["cold_ms"] / DEPTH, 4), "timing": "warm: 5 back-to-back launches per bounce (tree in L2, as inside a frame); cold: 256 MB L2 flush before each of 3 launches",
             "algorithmic_bytes_per_launch": round(ext["bytes"] / DEPTH), "mrays_per_s": round(ext["rays"] / (ext["ms"] * 1e-3) / 1e6, 1),
             "frac_cold": round(ext["bytes"] / (ext["cold_ms"] * 1e-3) / 1e9 / peak, 5),

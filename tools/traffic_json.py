@@ -42,6 +42,9 @@ out = {"capture": os.path.relpath(keep, ROOT) + " (tools/rc_ncu.sh: the extensio
        "l1_data_pipe_pct_per_bounce": [round(x, 1) for x in g("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed")],
        "l1_hit_pct_per_bounce": [round(x, 1) for x in g("l1tex__t_sector_hit_rate.pct")],
        "l2_hit_pct_per_bounce": [round(x, 1) for x in g("lts__t_sector_hit_rate.pct")],
-       "us_per_bounce_under_ncu": [round(x / 1e3, 1) for x in g("gpu__time_duration.sum")]}
+       "us_per_bounce_under_ncu": [round(x / 1e3, 1) for x in g("gpu__time_duration.sum")],
+       "note": "the stand-alone launch (no Logic) fetches the 64-byte ray + state block of every ray and uses the ray half: 61 MB of the traffic are state "
+               "records that the same kernel fused with Logic reads in the frame (there: 253 MB per launch at bounce 1 = 133 B per ray, "
+               "profiles/r02_frame_kernels.csv; caches flushed by ncu before every launch, so 28 MB of tree and leaf records are fetched again)"}
 json.dump(out, open(os.path.join(ROOT, "profiles", "raycast_traffic.json"), "w"), indent=1)
 print(json.dumps({k: out[k] for k in ("kernel_sources_sha16", "dram_bytes_per_launch", "active_lanes_mean")}))
