@@ -400,16 +400,15 @@ struct WalkWide {
             float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
             float tu, tv;
             float tt = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), r.o, r.d, tu, tv);
+            // The reference's test on the leaf's own box (what decides whether it ever sees this triangle) waits until finish(): one
+            // lane in 32 needs it here, and it is as long as half a box visit.  Until then the nearest triangle hit is provisional.
             if (tt > PTB_EPSILON && tt < limit) {
-                float tb = leaf_box_test(a, b, c, r.o, r.inv);
-                if (tb != -1.0f && tb < limit) {
-                    if (tt < t && tb < t) {                          // the reference's acceptance, src/kernels/ray_cast.cu:68,93-94
-                        second = fminf(second, t);
-                        t = tt; u = tu; v = tv;
-                        leaf = ~node;
-                    } else {
-                        second = fminf(second, tt);
-                    }
+                if (tt < t) {
+                    second = fminf(second, t);
+                    t = tt; u = tu; v = tv;
+                    leaf = ~node;
+                } else {
+                    second = fminf(second, tt);
                 }
             }
             node = PTB_NODE_NONE;
@@ -417,30 +416,36 @@ struct WalkWide {
     }
     template <class STACK>
     __device__ __forceinline__ Hit finish(const BvhDev& bvh, STACK& st) {
-        const bool ambiguous = second < 0.0f || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
-        if (ambiguous) {
+        bool ambiguous = second < 0.0f || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
+        Hit h;
+        h.prim = -1; h.mat = -1; h.t = t; h.u = u; h.v = v;
+        if (!ambiguous && leaf >= 0) {
+            // the winner stands if the reference reaches its leaf: its own box passes the reference's test with an entry distance
+            // below every best-so-far the reference can hold when it gets there (all of them beyond t * slack, else `second` says so).
+            // A winner that fails was never seen by the reference, and what it culled on the way is unknown: re-walk.
+            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)leaf;
+            F8 ab = ldg256(tp);
+            const float4 c = __ldg(tp + 2);
+            const float tb = leaf_box_test(ab.a, ab.b, c, r.o, r.inv);
+            ambiguous = !(tb != -1.0f && tb < t * PTB_WIDE_SLACK);
+            h.prim = __float_as_int(ab.a.w);
+            h.mat = __float_as_int(ab.b.w);
+        }
+        if (ambiguous) {     // the reference-order walk decides
             WalkBinary w;
             w.init(bvh, r.o, r.d);
             while (w.busy()) w.step(bvh, st);
             return w.h;
         }
-        Hit h;
-        h.prim = -1; h.mat = -1; h.t = t; h.u = u; h.v = v;
-        if (leaf >= 0) {
-            const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)leaf;
-            h.prim = __float_as_int(__ldg(tp).w);
-            h.mat = __float_as_int(__ldg(tp + 1).w);
-        }
         return h;
     }
 };
 
-// WalkAnyWide: trace_any_wide() cut at the loop body (visibility rays on the 4-wide quantised tree), for the persistent-lane
-// shadow kernel.  result: 0 nothing found (so far), 1 occluded, -1 not decidable here -> finish() takes the binary walk.
 struct WalkAnyWide {
     WideRay r;
     float tmax;
-    int node, sp, result;
+    int node, sp, result;                     // result 2: a triangle was hit, its leaf `cand` still owes the reference's box test (confirm())
+    int cand;
     __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
     __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
     __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o, Vec3 d, float tmax_) {
@@ -477,13 +482,20 @@ struct WalkAnyWide {
             float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
             float u, v;
             float t = triangle_test(Vec3(a.x, a.y, a.z), Vec3(b.x, b.y, b.z), Vec3(c.x, c.y, c.z), r.o, r.d, u, v);
+            if (t > PTB_EPSILON && t < __fsub_rn(tmax, PTB_EPSILON)) { result = 2; cand = ~node; }
             node = PTB_NODE_NONE;
-            if (t > PTB_EPSILON && t < __fsub_rn(tmax, PTB_EPSILON)) {
-                float tb = leaf_box_test(a, b, c, r.o, r.inv);          // the reference reaches this leaf iff its own box passes
-                if (tb != -1.0f && tmax > tb) result = 1;
-            }
         }
         if (result != 0) { node = PTB_NODE_NONE; sp = 0; }
+    }
+    // After the walk, converged: 1 occluded, 0 visible, -1 take the reference-order walk.  The reference reaches the hit triangle's
+    // leaf iff the leaf's own box passes its test; a hit that fails it was never seen by the reference, and the walk stopped there.
+    __device__ __forceinline__ int confirm(const BvhDev& bvh) const {
+        if (result != 2) return result;
+        const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)cand;
+        F8 ab = ldg256(tp);
+        const float4 c = __ldg(tp + 2);
+        const float tb = leaf_box_test(ab.a, ab.b, c, r.o, r.inv);
+        return (tb != -1.0f && tmax > tb) ? 1 : -1;
     }
 };
 
