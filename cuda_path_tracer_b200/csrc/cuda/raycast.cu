@@ -204,8 +204,9 @@ __global__ void __launch_bounds__(PTB_RC_THREADS, MINB) k_trace_shadow_pl(FrameD
                 if (w.busy()) w.step(f.bvh, st);
             n_done = __popc(__ballot_sync(0xffffffffu, !w.busy()));
         } while (n_done < want);
+        if (ray >= 0 && !w.busy()) w.confirm(f.bvh);        // a refused triangle hit: the lane is busy again and keeps its ray
         if (ray >= 0 && !w.busy()) {
-            int res = w.confirm(f.bvh);
+            int res = w.result;
             if (res < 0) res = trace_any<PTB_EXT_STACK>(f.bvh, w.r.o, w.r.d, w.tmax, stack + threadIdx.x, PTB_RC_THREADS);
             if (res == 0) {   // visible: AtomicAddVec3(&d_direct_image[pixel], radiance), src/kernels/ray_cast.cu:193-199
                 int slot = __ldg(&f.shadow.slot[ray]);

@@ -215,6 +215,11 @@ struct WalkBinary {
     Vec3 o, d, inv;
     Hit h;
     int node, sp;
+    // Boxes entered beyond `ub` are skipped.  FLT_MAX: the reference's walk.  A finite bound is for re-walks that already know the
+    // answer lies below it: the reference's decisions among the hits below the bound do not depend on what it met beyond it (its best
+    // so far is then either such a far hit or none, and every test a near hit has to pass -- t < best, box distance < best -- holds
+    // in both cases), and in trees under 32 levels its stack never aborts.
+    float ub;
     __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
     __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
     __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o_, Vec3 d_) {
@@ -222,6 +227,7 @@ struct WalkBinary {
         inv = Vec3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));
         h.prim = -1; h.mat = -1; h.t = FLT_MAX; h.u = 0.0f; h.v = 0.0f;
         sp = 0;
+        ub = FLT_MAX;
         node = (slab_test(bvh.root_min, bvh.root_max, o, inv) == -1.0f) ? PTB_NODE_NONE : 0;
     }
     template <class STACK>
@@ -243,8 +249,8 @@ struct WalkBinary {
             const NodePair nt = node_test(bvh.node + 4 * (size_t)node, o, inv);
             const float t_l = nt.t_l, t_r = nt.t_r;
             const int left = nt.left, right = nt.right;
-            bool hit_l = (t_l != -1.0f && t_l < h.t);
-            bool hit_r = (t_r != -1.0f && t_r < h.t);
+            bool hit_l = (t_l != -1.0f && t_l < h.t && t_l <= ub);
+            bool hit_r = (t_r != -1.0f && t_r < h.t && t_r <= ub);
             if (hit_l && hit_r) {
                 bool left_first = t_l < t_r;
                 st.set(sp++, left_first ? right : left);
@@ -368,7 +374,9 @@ struct WalkWide {
         if (!r.ok) second = -1.0f;
         node = r.ok ? 0 : PTB_NODE_NONE;
     }
-    template <class STACK>
+    // EXACT: the leaf-box test inside the walk (a triangle the reference cannot see is never a candidate); the scheduler's loop runs
+    // EXACT = false and finish() verifies the winner.
+    template <class STACK, bool EXACT = false>
     __device__ __forceinline__ void step(const BvhDev& bvh, STACK& st) {
         if (node == PTB_NODE_NONE) node = st.get(--sp);
         const float limit = t * PTB_WIDE_SLACK;
@@ -403,12 +411,20 @@ struct WalkWide {
             // The reference's test on the leaf's own box (what decides whether it ever sees this triangle) waits until finish(): one
             // lane in 32 needs it here, and it is as long as half a box visit.  Until then the nearest triangle hit is provisional.
             if (tt > PTB_EPSILON && tt < limit) {
-                if (tt < t) {
-                    second = fminf(second, t);
-                    t = tt; u = tu; v = tv;
-                    leaf = ~node;
-                } else {
-                    second = fminf(second, tt);
+                bool seen = true, best = tt < t;
+                if (EXACT) {
+                    const float tb = leaf_box_test(a, b, c, r.o, r.inv);
+                    seen = tb != -1.0f && tb < limit;
+                    best = best && tb < t;                           // the reference's acceptance, src/kernels/ray_cast.cu:68,93-94
+                }
+                if (seen) {
+                    if (best) {
+                        second = fminf(second, t);
+                        t = tt; u = tu; v = tv;
+                        leaf = ~node;
+                    } else {
+                        second = fminf(second, tt);
+                    }
                 }
             }
             node = PTB_NODE_NONE;
@@ -416,27 +432,45 @@ struct WalkWide {
     }
     template <class STACK>
     __device__ __forceinline__ Hit finish(const BvhDev& bvh, STACK& st) {
-        bool ambiguous = second < 0.0f || ((leaf >= 0) && (second <= t * PTB_WIDE_SLACK));
-        Hit h;
-        h.prim = -1; h.mat = -1; h.t = t; h.u = u; h.v = v;
-        if (!ambiguous && leaf >= 0) {
-            // the winner stands if the reference reaches its leaf: its own box passes the reference's test with an entry distance
-            // below every best-so-far the reference can hold when it gets there (all of them beyond t * slack, else `second` says so).
-            // A winner that fails was never seen by the reference, and what it culled on the way is unknown: re-walk.
+        // The winner stands if the reference reaches its leaf: its own box passes the reference's test with an entry distance below
+        // every best-so-far the reference can hold when it gets there (all of them beyond t * slack, else `second` says so).
+        bool verified = leaf < 0;
+        int prim = -1, mat = -1;
+        if (second >= 0.0f && leaf >= 0) {
             const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)leaf;
             F8 ab = ldg256(tp);
             const float4 c = __ldg(tp + 2);
             const float tb = leaf_box_test(ab.a, ab.b, c, r.o, r.inv);
-            ambiguous = !(tb != -1.0f && tb < t * PTB_WIDE_SLACK);
-            h.prim = __float_as_int(ab.a.w);
-            h.mat = __float_as_int(ab.b.w);
+            prim = __float_as_int(ab.a.w);
+            mat = __float_as_int(ab.b.w);
+            verified = tb != -1.0f && tb < t * PTB_WIDE_SLACK;
         }
-        if (ambiguous) {     // the reference-order walk decides
+        if (second >= 0.0f && !verified) {
+            // A winner that fails was never seen by the reference, and what it culled on the way is unknown (one ray in 200 on the
+            // bench scene: grazing hits on flat, axis-aligned triangles): this walk again, with the test inside it.
+            t = FLT_MAX; u = 0.0f; v = 0.0f; second = FLT_MAX; leaf = -1;
+            sp = 0;
+            node = 0;
+            while (busy()) step<STACK, true>(bvh, st);
+            verified = true;
+            if (leaf >= 0) {
+                const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)leaf;
+                prim = __float_as_int(__ldg(tp).w);
+                mat = __float_as_int(__ldg(tp + 1).w);
+            }
+        }
+        // overflow / unusable reciprocal: the whole reference-order walk; another candidate within the slack of a verified winner: the
+        // reference's order decides between them, and nothing beyond them matters (WalkBinary::ub)
+        const bool near_tie = second >= 0.0f && leaf >= 0 && second <= t * PTB_WIDE_SLACK;
+        if (second < 0.0f || near_tie) {
             WalkBinary w;
             w.init(bvh, r.o, r.d);
+            if (near_tie) w.ub = t * (PTB_WIDE_SLACK * PTB_WIDE_SLACK);
             while (w.busy()) w.step(bvh, st);
             return w.h;
         }
+        Hit h;
+        h.prim = prim; h.mat = mat; h.t = t; h.u = u; h.v = v;
         return h;
     }
 };
@@ -447,7 +481,7 @@ struct WalkAnyWide {
     int node, sp, result;                     // result 2: a triangle was hit, its leaf `cand` still owes the reference's box test (confirm())
     int cand;
     __device__ __forceinline__ void reset() { node = PTB_NODE_NONE; sp = 0; }
-    __device__ __forceinline__ bool busy() const { return node != PTB_NODE_NONE || sp > 0; }
+    __device__ __forceinline__ bool busy() const { return result == 0 && (node != PTB_NODE_NONE || sp > 0); }
     __device__ __forceinline__ void init(const BvhDev& bvh, Vec3 o, Vec3 d, float tmax_) {
         r = wide_setup(bvh, o, d);
         tmax = tmax_;
@@ -485,17 +519,17 @@ struct WalkAnyWide {
             if (t > PTB_EPSILON && t < __fsub_rn(tmax, PTB_EPSILON)) { result = 2; cand = ~node; }
             node = PTB_NODE_NONE;
         }
-        if (result != 0) { node = PTB_NODE_NONE; sp = 0; }
     }
-    // After the walk, converged: 1 occluded, 0 visible, -1 take the reference-order walk.  The reference reaches the hit triangle's
-    // leaf iff the leaf's own box passes its test; a hit that fails it was never seen by the reference, and the walk stopped there.
-    __device__ __forceinline__ int confirm(const BvhDev& bvh) const {
-        if (result != 2) return result;
+    // A lane that stopped at a triangle hit (result 2), in the converged part of the scheduler's loop: the reference reaches that
+    // triangle's leaf iff the leaf's own box passes its test.  Passed: occluded (1).  Failed: the reference never saw the triangle;
+    // the lane's stack is untouched, so it simply goes on with its walk (result 0, busy() again unless nothing is left).
+    __device__ __forceinline__ void confirm(const BvhDev& bvh) {
+        if (result != 2) return;
         const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)cand;
         F8 ab = ldg256(tp);
         const float4 c = __ldg(tp + 2);
         const float tb = leaf_box_test(ab.a, ab.b, c, r.o, r.inv);
-        return (tb != -1.0f && tmax > tb) ? 1 : -1;
+        result = (tb != -1.0f && tmax > tb) ? 1 : 0;
     }
 };
 
