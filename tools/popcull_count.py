@@ -1,5 +1,6 @@
+"""How many popped stack entries of the 4-wide closest-hit walk could have been culled by their entry distance (needs a\n-DPTB_WIDE_DEBUG -DPTB_EXP_POPCULL build of raycast.cu with the counting variant of WalkWide::step; profiles/r02_raycast_notes.md section 5)."""
 import ctypes as C, sys
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 import cuda_path_tracer_b200 as ptb
 from cuda_path_tracer_b200 import scenegen, capi
 r = ptb.Renderer(ptb.Scene(scenegen.fireplace("/tmp/dbg_fire", res=(1920, 1080))[0]))

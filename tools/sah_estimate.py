@@ -1,5 +1,6 @@
+"""Summed internal surface area of the LBVH against a PLOC tree (radius argv[2]) over the same Morton-sorted leaves, numpy, CPU only:\nwould a better tree under the 4-wide records pay?  (profiles/r02_raycast_notes.md section 5: 0.99x / 0.88x -- no.)  Uses the CPU oracle: a tool, not product."""
 import sys, time
-sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
+ROOT = __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, ROOT + "/tests")
 import numpy as np
 import cuda_path_tracer_b200 as ptb
 from cuda_path_tracer_b200 import scenegen
