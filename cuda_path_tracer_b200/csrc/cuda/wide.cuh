@@ -402,7 +402,8 @@ struct WalkWide {
             }
             if (sp > PTB_WIDE_STACK) { sp = PTB_WIDE_STACK; second = -1.0f; }   // entries dropped: finish() re-walks
             node = (key[0] != FLT_MAX) ? lnk[0] : PTB_NODE_NONE;
-        } else {
+        }
+        if (node < 0) {                                             // a popped leaf, or the nearest child just chosen: same step
             const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
             F8 ab = ldg256(tp);
             float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);
@@ -510,7 +511,8 @@ struct WalkAnyWide {
                 }
             }
             if (sp > PTB_WIDE_STACK) result = -1;                       // PTB_WIDE_PUSHES spare entries took the excess
-        } else {
+        }
+        if (node < 0 && result == 0) {                              // a popped leaf, or the first child just chosen: same step
             const float4* tp = bvh.tri + PTB_TRI_STRIDE * (size_t)(~node);
             F8 ab = ldg256(tp);
             float4 a = ab.a, b = ab.b, c = __ldg(tp + 2);

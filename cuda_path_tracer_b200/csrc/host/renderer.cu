@@ -338,7 +338,7 @@ int ptb_init(const ptb_scene* scene, const ptb_config* cfg_in, ptb_renderer** ou
         r->launch.rc_mode = knob("PTB_RC_MODE", 3);
         r->launch.rc_refill = knob("PTB_RC_REFILL", 24);
         r->launch.rc_stack = knob("PTB_RC_STACK", 0);
-        r->launch.rc_minb = knob("PTB_RC_MINB", 9);
+        r->launch.rc_minb = knob("PTB_RC_MINB", 8);
         r->launch.rc_steps = knob("PTB_RC_STEPS", 4);
         r->launch.rc_b0 = knob("PTB_RC_B0", 0);
         r->launch.mega_regen = knob("PTB_MEGA_REGEN", 1);
